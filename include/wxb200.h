@@ -1,0 +1,153 @@
+/* wxb200.h -- C ABI of the B200-native cubed-sphere DFR right-hand side and FD Jacobian-vector product.
+ *
+ * This is the drop-in boundary for WxFactory's hot path.  The reference has no FFI for this path (it is
+ * numpy); the entry points below are what a binding for it would call, each one citing the reference
+ * interface it replaces (paths relative to the reference root):
+ *
+ *   wxb_create        <- RHS.__init__ / RhsShallowWater.__init__ receiving geometry, operators, metric
+ *                        (wx_factory/rhs/rhs.py:14-35, wx_factory/rhs/rhs_sw.py:18-36) and the halo tables of
+ *                        ProcessTopology.__init__ (wx_factory/process_topology.py:50-267)
+ *   wxb_rhs           <- RHS.__call__(q) -> dq/dt  (wx_factory/rhs/rhs.py:75-122),
+ *                        RhsShallowWater.__call__   (wx_factory/rhs/rhs_sw.py:38-56)
+ *   wxb_jvp           <- matvec_fun(vec, dt, Q, rhs, rhs_handle, "fd") (wx_factory/solvers/matvec.py:36-68)
+ *                        and matvec_rat (wx_factory/solvers/matvec.py:76-88)
+ *   wxb_traces / wxb_finish
+ *                     <- the two halves of RHS.__call__ either side of the halo exchange:
+ *                        solution_extrapolation + start_communication (wx_factory/rhs/rhs_dfr.py:50-71,141-172)
+ *                        and end_communication ... forcing_terms     (wx_factory/rhs/rhs_dfr.py:174-313)
+ *   wxb_rhs_host / wxb_jvp_host
+ *                     <- the same calls with HOST buffers (what the reference's CPU integrators hold)
+ *   wxb_timings       <- RHS.retrieve_last_times / Device.elapsed (wx_factory/rhs/rhs.py:72-73,
+ *                        wx_factory/device/device.py:201-214)
+ *   wxb_destroy, wxb_last_error, wxb_version : lifetime / error convention (the reference raises Python
+ *                        exceptions: wx_factory/rhs/rhs_selector.py:44,83)
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative WXB_E*
+ * code and never throws; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); work is
+ * enqueued asynchronously on `stream` (the *_host variants synchronise before returning).  A handle is not
+ * re-entrant: calls on one handle must be serialised by the caller, as in the reference
+ * (wx_factory/rhs/rhs_dfr.py:148-172 keeps request state between start/end_communication).
+ *
+ * State layout (device or host, float64, C order): the slabs this handle owns, concatenated; each slab is
+ * the reference's per-rank array  (num_var, nz, ny_slab, nx, n^3)  [Euler]  /  (num_var, ny_slab, nx, n^2)  [SW]
+ * (wx_factory/geometry/cubed_sphere_3d.py:186-190, cubed_sphere_2d.py:161-170).
+ */
+#ifndef WXB200_H
+#define WXB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WXB_VERSION 1
+#define WXB_MAX_SLABS 8
+#define WXB_MAX_N 6
+
+#define WXB_OK 0
+#define WXB_EINVAL (-1)  /* bad argument / unsupported size          */
+#define WXB_ECUDA (-2)   /* a CUDA runtime call or kernel failed     */
+#define WXB_ENOMEM (-3)  /* device or host allocation failed         */
+#define WXB_ESTATE (-4)  /* call sequence error (e.g. finish before traces) */
+
+#define WXB_EQ_EULER3D 0
+#define WXB_EQ_SHALLOW_WATER 1
+
+#define WXB_JVP_FD 0  /* dt * (RHS(Q + eps v) - rhs0) / eps                  */
+#define WXB_JVP_RAT 1 /* v - 0.5 * dt * (RHS(Q + eps v) - rhs0) / eps        */
+
+typedef struct wxb_handle wxb_handle;
+
+typedef struct {
+    int32_t equations;             /* WXB_EQ_*                                                        */
+    int32_t n;                     /* num_solpts, 2..WXB_MAX_N                                        */
+    int32_t nz;                    /* elements per column (1 for shallow water)                       */
+    int32_t nx;                    /* elements per slab row (= elements per panel side)               */
+    int32_t nslabs;                /* slabs owned by this handle                                      */
+    int32_t slab_ny[WXB_MAX_SLABS];/* rows of elements in each slab                                   */
+    int32_t nghost;                /* ghost (column,face) trace records received from other handles   */
+    int32_t nsend;                 /* (column,face) trace records this handle packs for other handles */
+    int32_t nxform;                /* rows of the panel-edge vector transform table                   */
+    int32_t advection_only;        /* Euler case_number < 13: RHS is identically zero                 */
+    int32_t has_damping;           /* Euler: Rayleigh damping arrays present (DCMIP 2-1 / 2-2)        */
+    int32_t has_topo;              /* SW: topography arrays present (Williamson 5)                    */
+    double damp_tau0;
+} wxb_config;
+
+/* All pointers are HOST pointers; wxb_create copies what it needs to the device.
+ * E = local elements (sum over slabs of nz*ny_s*nx), C = local columns (sum of ny_s*nx),
+ * P = n^3 (n^2 for SW), F = n^2 (n for SW). */
+typedef struct {
+    /* 1-D operator blocks (DFROperators, wx_factory/geometry/operators.py:55-80,144-145) */
+    const double* ext_w;  /* [n]    */
+    const double* ext_e;  /* [n]    */
+    const double* diff;   /* [n*n]  diff_solpt, row-major: out[i'] = sum_i diff[i'*n+i] f[i] */
+    const double* corr;   /* [n*2]  correction, column 0 = min-side face, 1 = max-side       */
+    const double* hfilt;  /* [n*n]  highfilter (Euler only)                                  */
+    /* interior metric, local element order */
+    const double* sqrtg;      /* [E*P]                                   */
+    const double* h;          /* Euler [6][E*P] (11,12,13,22,23,33); SW [3][E*P] (11,12,22) */
+    const double* chris;      /* Euler [27][E*P]; SW [8][E*P]            */
+    const double* inv_dzdeta; /* Euler [E*P]                             */
+    const double* damp;       /* Euler, optional [4][E*P]: profile, u1ref, u2ref, u3ref */
+    const double* topo;       /* SW, optional [3][E*P]: hsurf, dzdx1, dzdx2             */
+    /* interface metric once per physical face, slab after slab:
+     * Euler comps = 4 (sqrtG, h^{d1}, h^{d2}, h^{d3}); SW comps = 3 (sqrtG, H^{1d}.. see problem.py)
+     *   fm_i: per slab [comps][nz][ny_s][nx+1][F];  fm_j: [comps][nz][ny_s+1][nx][F];  fm_k: [comps][nz+1][ny_s][nx][F] */
+    const double* fm_i;
+    const double* fm_j;
+    const double* fm_k;   /* Euler only */
+    const double* topo_itf; /* SW optional: hsurf on faces: i-faces then j-faces, two-sided values
+                               [ (own side, neighbour side) ... ] see csrc/sw2d.cu */
+    /* horizontal connectivity, pull model: for face f in (W,E,S,N) of local column c the neighbour trace of
+     * variable v, level k, face point pt lives at  trace[((base + v*vstride + k*kstride) * F) + pt']:
+     *   nbr[(f*C + c)*4 + {0,1,2,3}] = base, kstride, vstride, flags
+     *   flags bit0: reverse the along-edge node index; bits 8..: 1 + row of `xform` (0 = identity) */
+    const int32_t* nbr;     /* [4*C*4] */
+    const double* xform;    /* [nxform][n][4]: 2x2 matrix (m11,m12,m21,m22) applied to (var1,var2) per along-edge node */
+    const int32_t* send;    /* [nsend]: col*4 + face of each record to pack, in send-buffer order */
+} wxb_static_arrays;
+
+int wxb_version(void);
+
+int wxb_create(const wxb_config* cfg, const wxb_static_arrays* arrays, int device, wxb_handle** out);
+int wxb_destroy(wxb_handle* h);
+const char* wxb_last_error(const wxb_handle* h); /* h may be NULL: last create error */
+
+/* sizes, in doubles */
+int64_t wxb_state_size(const wxb_handle* h);      /* num_var * E * P                                  */
+int64_t wxb_send_size(const wxb_handle* h);       /* nsend  * num_var * nz * F                         */
+int64_t wxb_recv_size(const wxb_handle* h);       /* nghost * num_var * nz * F                         */
+double* wxb_send_buffer(wxb_handle* h);           /* device pointer, contiguous, record-major          */
+double* wxb_recv_buffer(wxb_handle* h);           /* device pointer (the ghost tail of the trace array) */
+
+/* One whole evaluation on a handle without remote neighbours (nghost == 0): dq = RHS(q). */
+int wxb_rhs(wxb_handle* h, const double* q, double* dq, void* stream);
+
+/* out = JVP(v) around q with cached rhs0 = RHS(q) (mode WXB_JVP_*), base+perturbed fused in one pass:
+ * the perturbed state q + eps*v is formed in registers, the epilogue applies dt*(.-rhs0)/eps [and v - 0.5*..]. */
+int wxb_jvp(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode,
+            double* out, void* stream);
+
+/* Split form for handles with remote neighbours.  wxb_traces extrapolates q (+ eps*v if v != NULL) to all
+ * faces and packs the records listed in `send` into wxb_send_buffer; the caller moves them into the peers'
+ * wxb_recv_buffer (NCCL / peer copy), then calls wxb_finish with the same q, v, eps.
+ * part: 0 = all elements, 1 = only elements that do not read ghost records (may run before the exchange
+ * has completed), 2 = only elements that do. */
+int wxb_traces(wxb_handle* h, const double* q, const double* v, double eps, void* stream);
+int wxb_finish(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps,
+               int mode /* -1 = plain RHS */, int part, double* out, void* stream);
+
+/* Same as wxb_rhs / wxb_jvp with HOST buffers: H2D copy, kernels, D2H copy, synchronise. */
+int wxb_rhs_host(wxb_handle* h, const double* q_host, double* dq_host);
+int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, const double* rhs0_host, double dt,
+                 double eps, int mode, double* out_host);
+
+/* Device time of the last evaluation's kernels in ms: [0] traces(+pack), [1] main, [2] total. */
+int wxb_timings(wxb_handle* h, float out_ms[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,114 @@
+"""Parity of the CUDA path (through the C ABI) with the reference's golden vectors and with the oracle.
+
+Tolerances (FP64, BASELINE.json north_star: 1e-12 relative per RHS evaluation):
+  RHS_TOL  relative L2 error of the whole RHS and of every variable, vs the reference's own output
+  JVP_TOL  FD-JVP error relative to dt*|rhs|/eps (the FD formula amplifies RHS rounding by 1/eps ~ 2900,
+           SURVEY 7.3), vs the reference's matvec_fun(..., 'fd') / matvec_rat outputs
+"""
+
+import numpy
+import pytest
+
+from conftest import GOLDEN_NAMES
+
+pytestmark = pytest.mark.gpu
+
+RHS_TOL = 1e-12
+JVP_TOL = 1e-12
+
+
+def rel(a, b):
+    nb = numpy.linalg.norm(b)
+    return numpy.linalg.norm(a - b) / (nb if nb > 0 else 1.0)
+
+
+@pytest.fixture(scope="module")
+def rhs_cache(golden):
+    from wxfactory_b200 import RhsB200
+
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            prob, ex = golden(name)
+            cache[name] = (RhsB200(prob), prob, ex)
+        return cache[name]
+
+    yield get
+    for r, _, _ in cache.values():
+        r.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_rhs_matches_reference_host_path(rhs_cache, name):
+    rhs, prob, ex = rhs_cache(name)
+    out = rhs(ex["Q0"])
+    assert isinstance(out, numpy.ndarray) and out.shape == ex["Q0"].shape
+    assert rel(out, ex["rhs0"]) <= RHS_TOL
+    for v in range(prob.num_var):
+        assert rel(out[:, v], ex["rhs0"][:, v]) <= RHS_TOL * 10, f"variable {v}"
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_rhs_matches_reference_device_path(rhs_cache, name):
+    import torch
+
+    rhs, prob, ex = rhs_cache(name)
+    q = torch.from_numpy(ex["Q0"]).cuda()
+    out = rhs(q.view(-1))  # flattened Krylov-style input keeps its shape
+    assert out.shape == (q.numel(),) and out.is_cuda
+    assert rel(out.cpu().numpy().reshape(ex["rhs0"].shape), ex["rhs0"]) <= RHS_TOL
+    assert torch.equal(q, torch.from_numpy(ex["Q0"]).cuda()), "input must not be modified"
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_jvp_matches_reference(rhs_cache, name):
+    import torch
+
+    from wxfactory_b200 import EPS_FD, matvec_fun, matvec_rat
+
+    rhs, prob, ex = rhs_cache(name)
+    dt = float(ex["dt"])
+    scale = dt * numpy.linalg.norm(ex["rhs0"]) / EPS_FD
+    # host arrays, the reference's positional signature
+    fd = matvec_fun(ex["v"].ravel(), dt, ex["Q0"], ex["rhs0"], rhs.full, "fd")
+    assert fd.shape == (ex["Q0"].size,)
+    assert numpy.linalg.norm(fd - ex["jv_fd"].ravel()) <= JVP_TOL * scale
+    rat = matvec_rat(ex["v"].ravel(), dt, ex["Q0"], ex["rhs0"], rhs)
+    assert numpy.linalg.norm(rat - ex["jv_rat"].ravel()) <= JVP_TOL * max(scale, numpy.linalg.norm(ex["v"]))
+    # device tensors
+    dev = lambda a: torch.from_numpy(numpy.ascontiguousarray(a)).cuda()  # noqa: E731
+    fd_d = rhs.jvp(dev(ex["v"]), dt, dev(ex["Q0"]), dev(ex["rhs0"]), mode="fd")
+    assert numpy.linalg.norm(fd_d.cpu().numpy() - ex["jv_fd"].ravel()) <= JVP_TOL * scale
+
+
+@pytest.mark.parametrize("name", ["dcmip21", "case6"])
+def test_perturbed_states_match_oracle(rhs_cache, name):
+    """Seeded random perturbations of the golden state, CUDA vs oracle (not only the analytic initial state)."""
+    from oracle import jvp_oracle
+
+    rhs, prob, ex = rhs_cache(name)
+    orc = jvp_oracle.make_oracle(prob)
+    rng = numpy.random.default_rng(11)
+    for _ in range(3):
+        Q = ex["Q0"] * (1.0 + 1e-3 * rng.standard_normal(ex["Q0"].shape)) + 1e-6 * rng.standard_normal(ex["Q0"].shape)
+        with numpy.errstate(all="ignore"):
+            want = orc.rhs(Q)
+        assert rel(rhs(Q), want) <= RHS_TOL
+
+
+def test_complex_state_is_rejected(rhs_cache):
+    rhs, prob, ex = rhs_cache("dcmip21")
+    with pytest.raises(TypeError):
+        rhs(ex["Q0"].astype(numpy.complex128))
+    with pytest.raises(ValueError):
+        rhs(ex["Q0"].ravel()[:-1])
+
+
+def test_timings_vocabulary(rhs_cache):
+    rhs, prob, ex = rhs_cache("dcmip21")
+    rhs.clear_timings()
+    rhs(ex["Q0"])
+    rhs(ex["Q0"])
+    rhs.retrieve_last_times()
+    assert len(rhs.timings) >= 1 and all(t[2] > 0 for t in rhs.timings)

@@ -1,0 +1,143 @@
+"""ctypes binding of libwxb200.so (include/wxb200.h).  No torch types cross this boundary.
+
+The product path has no CPU fallback: if the library is missing or no CUDA device is present the calls
+raise (``RuntimeError``), they never route through numpy.
+"""
+
+import ctypes
+import os
+
+import numpy
+
+from . import build as _build
+
+WXB_MAX_SLABS = 8
+EQ_EULER3D, EQ_SW = 0, 1
+JVP_FD, JVP_RAT = 0, 1
+
+c_double_p = ctypes.POINTER(ctypes.c_double)
+c_int32_p = ctypes.POINTER(ctypes.c_int32)
+
+
+class WxbConfig(ctypes.Structure):
+    _fields_ = [
+        ("equations", ctypes.c_int32),
+        ("n", ctypes.c_int32),
+        ("nz", ctypes.c_int32),
+        ("nx", ctypes.c_int32),
+        ("nslabs", ctypes.c_int32),
+        ("slab_ny", ctypes.c_int32 * WXB_MAX_SLABS),
+        ("nghost", ctypes.c_int32),
+        ("nsend", ctypes.c_int32),
+        ("nxform", ctypes.c_int32),
+        ("advection_only", ctypes.c_int32),
+        ("has_damping", ctypes.c_int32),
+        ("has_topo", ctypes.c_int32),
+        ("damp_tau0", ctypes.c_double),
+    ]
+
+
+_ARRAY_FIELDS = [
+    ("ext_w", c_double_p),
+    ("ext_e", c_double_p),
+    ("diff", c_double_p),
+    ("corr", c_double_p),
+    ("hfilt", c_double_p),
+    ("sqrtg", c_double_p),
+    ("h", c_double_p),
+    ("chris", c_double_p),
+    ("inv_dzdeta", c_double_p),
+    ("damp", c_double_p),
+    ("topo", c_double_p),
+    ("fm_i", c_double_p),
+    ("fm_j", c_double_p),
+    ("fm_k", c_double_p),
+    ("topo_itf", c_double_p),
+    ("nbr", c_int32_p),
+    ("xform", c_double_p),
+    ("send", c_int32_p),
+]
+
+
+class WxbStaticArrays(ctypes.Structure):
+    _fields_ = _ARRAY_FIELDS
+
+
+EXPORTS = [
+    "wxb_version",
+    "wxb_create",
+    "wxb_destroy",
+    "wxb_last_error",
+    "wxb_state_size",
+    "wxb_send_size",
+    "wxb_recv_size",
+    "wxb_send_buffer",
+    "wxb_recv_buffer",
+    "wxb_rhs",
+    "wxb_jvp",
+    "wxb_traces",
+    "wxb_finish",
+    "wxb_rhs_host",
+    "wxb_jvp_host",
+    "wxb_timings",
+]
+
+_lib = None
+
+
+def library_path():
+    return _build.LIB
+
+
+def load():
+    """Load (building first if the sources are newer) and type the C ABI."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if not os.path.exists(path):
+        path = _build.build()
+    lib = ctypes.CDLL(path)
+    vp, i32, i64, dbl = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
+    lib.wxb_version.restype = i32
+    lib.wxb_create.argtypes = [ctypes.POINTER(WxbConfig), ctypes.POINTER(WxbStaticArrays), i32, ctypes.POINTER(vp)]
+    lib.wxb_destroy.argtypes = [vp]
+    lib.wxb_last_error.argtypes = [vp]
+    lib.wxb_last_error.restype = ctypes.c_char_p
+    for f in ("wxb_state_size", "wxb_send_size", "wxb_recv_size"):
+        getattr(lib, f).argtypes = [vp]
+        getattr(lib, f).restype = i64
+    for f in ("wxb_send_buffer", "wxb_recv_buffer"):
+        getattr(lib, f).argtypes = [vp]
+        getattr(lib, f).restype = vp
+    lib.wxb_rhs.argtypes = [vp, vp, vp, vp]
+    lib.wxb_jvp.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp, vp]
+    lib.wxb_traces.argtypes = [vp, vp, vp, dbl, vp]
+    lib.wxb_finish.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, i32, vp, vp]
+    lib.wxb_rhs_host.argtypes = [vp, vp, vp]
+    lib.wxb_jvp_host.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp]
+    lib.wxb_timings.argtypes = [vp, ctypes.POINTER(ctypes.c_float * 3)]
+    _lib = lib
+    return lib
+
+
+class WxbError(RuntimeError):
+    pass
+
+
+def check(lib, handle, code, what):
+    if code != 0:
+        msg = lib.wxb_last_error(handle)
+        msg = msg.decode() if msg else ""
+        exc = ValueError if code == -1 else WxbError
+        raise exc(f"{what} failed ({code}): {msg}")
+
+
+def as_f64(a):
+    return numpy.ascontiguousarray(a, dtype=numpy.float64)
+
+
+def ptr(a, typ=c_double_p):
+    if a is None:
+        return typ()
+    return a.ctypes.data_as(typ)

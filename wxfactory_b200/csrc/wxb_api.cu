@@ -1,0 +1,472 @@
+// C ABI of libwxb200.so (see include/wxb200.h for the contract and the reference interfaces replaced).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "wxb_internal.cuh"
+
+namespace {
+
+char g_create_err[512] = "";
+
+void set_err(wxb_handle* h, const char* fmt, ...) {
+    char* dst = h ? h->err : g_create_err;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+}
+
+#define CU(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t _e = (call);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            set_err(h, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return _e == cudaErrorMemoryAllocation ? WXB_ENOMEM : WXB_ECUDA;                  \
+        }                                                                                     \
+    } while (0)
+
+template <typename T>
+int upload(wxb_handle* h, T** dst, const T* src, size_t count) {
+    *dst = nullptr;
+    if (count == 0) return WXB_OK;
+    if (!src) {
+        set_err(h, "missing static array (%zu elements expected)", count);
+        return WXB_EINVAL;
+    }
+    CU(cudaMalloc((void**)dst, count * sizeof(T)));
+    CU(cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice));
+    return WXB_OK;
+}
+
+#define UP(dst, src, count)                          \
+    do {                                             \
+        int _r = upload(h, &(dst), (src), (count));  \
+        if (_r != WXB_OK) return _r;                 \
+    } while (0)
+
+int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
+    const bool euler = cfg->equations == WXB_EQ_EULER3D;
+    const int n = cfg->n;
+    h->n = n;
+    h->nvar = euler ? 5 : 3;
+    h->P = euler ? n * n * n : n * n;
+    h->F = euler ? n * n : n;
+    h->nfaces = euler ? 6 : 4;
+    const int nz = euler ? cfg->nz : 1;
+    const int nx = cfg->nx;
+    const int ncomp = euler ? 4 : 3;
+    SlabTab& st = h->st;
+    memset(&st, 0, sizeof(st));
+    st.nslabs = cfg->nslabs;
+    long long oi = 0, oj = 0, ok = 0;
+    int eb = 0, cb = 0;
+    for (int s = 0; s < cfg->nslabs; ++s) {
+        const int ny = cfg->slab_ny[s];
+        if (ny <= 0) {
+            set_err(h, "slab %d has ny=%d", s, ny);
+            return WXB_EINVAL;
+        }
+        st.ny[s] = ny;
+        st.ebase[s] = eb;
+        st.cbase[s] = cb;
+        st.fmi[s] = oi;
+        st.fmj[s] = oj;
+        st.fmk[s] = ok;
+        eb += nz * ny * nx;
+        cb += ny * nx;
+        oi += (long long)ncomp * nz * ny * (nx + 1) * h->F;
+        oj += (long long)ncomp * nz * (ny + 1) * nx * h->F;
+        ok += (long long)ncomp * (nz + 1) * ny * nx * h->F;
+    }
+    for (int s = cfg->nslabs; s <= WXB_MAX_SLABS; ++s) {
+        st.ebase[s] = eb;
+        st.cbase[s] = cb;
+    }
+    h->E = eb;
+    h->C = cb;
+    const size_t EP = (size_t)h->E * h->P;
+
+    const int nops = euler ? 4 * n + 2 * n * n : 4 * n + n * n;
+    std::vector<double> ops(nops, 0.0);
+    if (!A->ext_w || !A->ext_e || !A->diff || !A->corr || (euler && !A->hfilt)) {
+        set_err(h, "missing operator block");
+        return WXB_EINVAL;
+    }
+    memcpy(&ops[0], A->ext_w, n * sizeof(double));
+    memcpy(&ops[n], A->ext_e, n * sizeof(double));
+    memcpy(&ops[2 * n], A->diff, n * n * sizeof(double));
+    memcpy(&ops[2 * n + n * n], A->corr, 2 * n * sizeof(double));
+    if (euler) memcpy(&ops[4 * n + n * n], A->hfilt, n * n * sizeof(double));
+    UP(h->d_ops, ops.data(), (size_t)nops);
+
+    UP(h->d_sqrtg, A->sqrtg, EP);
+    UP(h->d_h, A->h, (euler ? 6 : 3) * EP);
+    UP(h->d_chris, A->chris, (euler ? 27 : 8) * EP);
+    if (euler) UP(h->d_idz, A->inv_dzdeta, EP);
+    if (euler && cfg->has_damping) UP(h->d_damp, A->damp, 4 * EP);
+    if (!euler && cfg->has_topo) {
+        UP(h->d_topo, A->topo, 3 * EP);
+        // hsurf on faces, two values (own side, other side) per face point: i-faces then j-faces
+        UP(h->d_topo_itf, A->topo_itf, (size_t)(oi / ncomp + oj / ncomp) * 2);
+    }
+    UP(h->d_fmi, A->fm_i, (size_t)oi);
+    UP(h->d_fmj, A->fm_j, (size_t)oj);
+    if (euler) UP(h->d_fmk, A->fm_k, (size_t)ok);
+    {
+        int4* tmp = nullptr;
+        int r = upload(h, (int32_t**)&tmp, A->nbr, (size_t)4 * h->C * 4);
+        if (r != WXB_OK) return r;
+        h->d_nbr = tmp;
+    }
+    UP(h->d_xform, A->xform, (size_t)cfg->nxform * n * 4);
+    UP(h->d_send, A->send, (size_t)cfg->nsend);
+
+    // trace array: local part [nvar][nfaces][E][F], then ghost records [rec][nvar][nz][F]
+    h->trace_local = (int64_t)h->nvar * h->nfaces * h->E * h->F;
+    const int64_t ghost = (int64_t)cfg->nghost * h->nvar * nz * h->F;
+    CU(cudaMalloc((void**)&h->d_trace, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
+    CU(cudaMemset(h->d_trace, 0, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
+    if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->nvar * nz * h->F * sizeof(double)));
+
+    // inner / outer element lists: an element is "outer" if one of its horizontal faces reads a ghost record
+    if (cfg->nghost > 0) {
+        std::vector<int> inner, outer;
+        const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
+        for (int s = 0; s < cfg->nslabs; ++s) {
+            const int ny = st.ny[s];
+            for (int k = 0; k < nz; ++k)
+                for (int cl = 0; cl < ny * nx; ++cl) {
+                    const int c = st.cbase[s] + cl;
+                    bool g = false;
+                    for (int f = 0; f < 4; ++f) g = g || (A->nbr[((size_t)f * h->C + c) * 4] >= ghost_base);
+                    (g ? outer : inner).push_back(st.ebase[s] + k * ny * nx + cl);
+                }
+        }
+        h->n_inner = (int)inner.size();
+        h->n_outer = (int)outer.size();
+        UP(h->d_elist_inner, inner.data(), inner.size());
+        UP(h->d_elist_outer, outer.data(), outer.size());
+    }
+    for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev[i]));
+    return WXB_OK;
+}
+
+void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, const double* rhs0, double dt, double eps,
+               int mode, double* out) {
+    memset(&a, 0, sizeof(a));
+    a.q = q;
+    a.v = v;
+    a.eps = v ? eps : 0.0;
+    a.rhs0 = rhs0;
+    a.dt = dt;
+    a.mode = mode;
+    a.out = out;
+    a.trace = h->d_trace;
+    a.sendbuf = h->d_sendbuf;
+    a.sqrtg = h->d_sqrtg;
+    a.h = h->d_h;
+    a.chris = h->d_chris;
+    a.idz = h->d_idz;
+    a.damp = h->d_damp;
+    a.topo = h->d_topo;
+    a.fmi = h->d_fmi;
+    a.fmj = h->d_fmj;
+    a.fmk = h->d_fmk;
+    a.topo_itf = h->d_topo_itf;
+    a.nbr = h->d_nbr;
+    a.xform = h->d_xform;
+    a.send = h->d_send;
+    a.ops = h->d_ops;
+    a.elist = nullptr;
+    a.nelist = 0;
+    a.E = h->E;
+    a.C = h->C;
+    a.nz = h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1;
+    a.nx = h->cfg.nx;
+    a.nsend = h->cfg.nsend;
+    a.has_damp = h->cfg.has_damping;
+    a.has_topo = h->cfg.has_topo;
+    a.tau0 = h->cfg.damp_tau0;
+    a.st = h->st;
+}
+
+int check_mode(wxb_handle* h, const double* q, const double* v, const double* rhs0, double eps, int mode, double* out) {
+    if (!q || !out) {
+        set_err(h, "null state/output pointer");
+        return WXB_EINVAL;
+    }
+    if (mode != -1 && mode != WXB_JVP_FD && mode != WXB_JVP_RAT) {
+        set_err(h, "unknown mode %d", mode);
+        return WXB_EINVAL;
+    }
+    if (mode >= 0 && (!v || !rhs0 || eps == 0.0)) {
+        set_err(h, "JVP needs v, rhs0 and a non-zero eps");
+        return WXB_EINVAL;
+    }
+    return WXB_OK;
+}
+
+int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaStream_t s) {
+    CU(cudaSetDevice(h->device));
+    if (h->cfg.equations == WXB_EQ_EULER3D && h->cfg.advection_only) {
+        h->traces_done = true;
+        return WXB_OK;
+    }
+    EvalArgs a;
+    fill_args(h, a, q, v, nullptr, 0.0, eps, -1, nullptr);
+    CU(cudaEventRecord(h->ev[0], s));
+    int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
+    if (r == 0) r = wxb_pack(a, h->nvar, h->F, s);
+    if (r != 0) {
+        set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return WXB_ECUDA;
+    }
+    CU(cudaEventRecord(h->ev[1], s));
+    h->traces_done = true;
+    return WXB_OK;
+}
+
+int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode,
+              int part, double* out, cudaStream_t s) {
+    CU(cudaSetDevice(h->device));
+    if (h->cfg.equations == WXB_EQ_EULER3D && h->cfg.advection_only) {
+        // rhs_dfr.py:307-313: every row is zeroed -> RHS == 0 (and so is the FD difference of two zero RHS)
+        if (part != 2) {
+            if (mode == WXB_JVP_RAT)
+                CU(cudaMemcpyAsync(out, v, (size_t)wxb_state_size(h) * sizeof(double), cudaMemcpyDeviceToDevice, s));
+            else
+                CU(cudaMemsetAsync(out, 0, (size_t)wxb_state_size(h) * sizeof(double), s));
+        }
+        return WXB_OK;
+    }
+    EvalArgs a;
+    fill_args(h, a, q, v, rhs0, dt, eps, mode, out);
+    if (part == 1 || part == 2) {
+        if (h->cfg.nghost == 0) {
+            if (part == 2) return WXB_OK;  // everything is inner
+        } else {
+            a.elist = part == 1 ? h->d_elist_inner : h->d_elist_outer;
+            a.nelist = part == 1 ? h->n_inner : h->n_outer;
+        }
+    } else if (part != 0) {
+        set_err(h, "part must be 0, 1 or 2");
+        return WXB_EINVAL;
+    }
+    int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_main(a, h->n, s) : wxb_sw_main(a, h->n, s);
+    if (r != 0) {
+        set_err(h, "main kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return WXB_ECUDA;
+    }
+    if (part != 1) {
+        CU(cudaEventRecord(h->ev[2], s));
+        h->timed = true;
+    }
+    return WXB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int wxb_version(void) { return WXB_VERSION; }
+
+const char* wxb_last_error(const wxb_handle* h) { return h ? h->err : g_create_err; }
+
+int wxb_create(const wxb_config* cfg, const wxb_static_arrays* arrays, int device, wxb_handle** out) {
+    wxb_handle* h = nullptr;
+    if (!cfg || !arrays || !out) {
+        set_err(h, "null argument");
+        return WXB_EINVAL;
+    }
+    *out = nullptr;
+    if (cfg->equations != WXB_EQ_EULER3D && cfg->equations != WXB_EQ_SHALLOW_WATER) {
+        set_err(h, "unknown equation set %d", cfg->equations);
+        return WXB_EINVAL;
+    }
+    if (cfg->n < 2 || cfg->n > WXB_MAX_N) {
+        set_err(h, "num_solpts %d outside 2..%d", cfg->n, WXB_MAX_N);
+        return WXB_EINVAL;
+    }
+    if (cfg->nslabs < 1 || cfg->nslabs > WXB_MAX_SLABS || cfg->nx < 1 ||
+        (cfg->equations == WXB_EQ_EULER3D && cfg->nz < 1)) {
+        set_err(h, "bad grid sizes (nslabs=%d nx=%d nz=%d)", cfg->nslabs, cfg->nx, cfg->nz);
+        return WXB_EINVAL;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_err(h, "no CUDA device available: this library has no CPU fallback");
+        cudaGetLastError();
+        return WXB_ECUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        set_err(h, "device %d out of range (%d devices)", device, ndev);
+        return WXB_EINVAL;
+    }
+    wxb_handle* nh = new (std::nothrow) wxb_handle();
+    if (!nh) return WXB_ENOMEM;
+    memset(nh, 0, sizeof(*nh));
+    nh->cfg = *cfg;
+    nh->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) {
+        set_err(h, "cudaSetDevice(%d) failed", device);
+        delete nh;
+        return WXB_ECUDA;
+    }
+    int r = build(nh, cfg, arrays);
+    if (r != WXB_OK) {
+        snprintf(g_create_err, sizeof(g_create_err), "%s", nh->err);
+        wxb_destroy(nh);
+        return r;
+    }
+    *out = nh;
+    return WXB_OK;
+}
+
+int wxb_destroy(wxb_handle* h) {
+    if (!h) return WXB_OK;
+    cudaSetDevice(h->device);
+    void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo,
+                    h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
+                    h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf,  h->d_q,           h->d_v,
+                    h->d_r0,   h->d_out};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    for (int i = 0; i < 3; ++i)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    delete h;
+    return WXB_OK;
+}
+
+int64_t wxb_state_size(const wxb_handle* h) { return h ? (int64_t)h->nvar * h->E * h->P : 0; }
+int64_t wxb_send_size(const wxb_handle* h) {
+    return h ? (int64_t)h->cfg.nsend * h->nvar * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
+}
+int64_t wxb_recv_size(const wxb_handle* h) {
+    return h ? (int64_t)h->cfg.nghost * h->nvar * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
+}
+double* wxb_send_buffer(wxb_handle* h) { return h ? h->d_sendbuf : nullptr; }
+double* wxb_recv_buffer(wxb_handle* h) { return h ? h->d_trace + h->trace_local : nullptr; }
+
+int wxb_traces(wxb_handle* h, const double* q, const double* v, double eps, void* stream) {
+    if (!h) return WXB_EINVAL;
+    if (!q) {
+        set_err(h, "null state pointer");
+        return WXB_EINVAL;
+    }
+    return do_traces(h, q, v, eps, (cudaStream_t)stream);
+}
+
+int wxb_finish(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode,
+               int part, double* out, void* stream) {
+    if (!h) return WXB_EINVAL;
+    int r = check_mode(h, q, v, rhs0, eps, mode, out);
+    if (r != WXB_OK) return r;
+    if (!h->traces_done) {
+        set_err(h, "wxb_finish called before wxb_traces");
+        return WXB_ESTATE;
+    }
+    r = do_finish(h, q, v, rhs0, dt, eps, mode, part, out, (cudaStream_t)stream);
+    if (part != 1) h->traces_done = false;
+    return r;
+}
+
+int wxb_rhs(wxb_handle* h, const double* q, double* dq, void* stream) {
+    if (!h) return WXB_EINVAL;
+    int r = check_mode(h, q, nullptr, nullptr, 0.0, -1, dq);
+    if (r != WXB_OK) return r;
+    if (h->cfg.nghost != 0) {
+        set_err(h, "handle has remote neighbours: use wxb_traces / exchange / wxb_finish");
+        return WXB_ESTATE;
+    }
+    r = do_traces(h, q, nullptr, 0.0, (cudaStream_t)stream);
+    if (r != WXB_OK) return r;
+    h->traces_done = false;
+    return do_finish(h, q, nullptr, nullptr, 0.0, 0.0, -1, 0, dq, (cudaStream_t)stream);
+}
+
+int wxb_jvp(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode,
+            double* out, void* stream) {
+    if (!h) return WXB_EINVAL;
+    if (mode < 0) {
+        set_err(h, "wxb_jvp needs mode WXB_JVP_FD or WXB_JVP_RAT");
+        return WXB_EINVAL;
+    }
+    int r = check_mode(h, q, v, rhs0, eps, mode, out);
+    if (r != WXB_OK) return r;
+    if (h->cfg.nghost != 0) {
+        set_err(h, "handle has remote neighbours: use wxb_traces / exchange / wxb_finish");
+        return WXB_ESTATE;
+    }
+    r = do_traces(h, q, v, eps, (cudaStream_t)stream);
+    if (r != WXB_OK) return r;
+    h->traces_done = false;
+    return do_finish(h, q, v, rhs0, dt, eps, mode, 0, out, (cudaStream_t)stream);
+}
+
+static int host_stage(wxb_handle* h) {
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    if (!h->d_q) {
+        CU(cudaSetDevice(h->device));
+        CU(cudaMalloc((void**)&h->d_q, bytes));
+        CU(cudaMalloc((void**)&h->d_v, bytes));
+        CU(cudaMalloc((void**)&h->d_r0, bytes));
+        CU(cudaMalloc((void**)&h->d_out, bytes));
+    }
+    return WXB_OK;
+}
+
+int wxb_rhs_host(wxb_handle* h, const double* q_host, double* dq_host) {
+    if (!h) return WXB_EINVAL;
+    if (!q_host || !dq_host) {
+        set_err(h, "null host pointer");
+        return WXB_EINVAL;
+    }
+    int r = host_stage(h);
+    if (r != WXB_OK) return r;
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    CU(cudaMemcpyAsync(h->d_q, q_host, bytes, cudaMemcpyHostToDevice, 0));
+    r = wxb_rhs(h, h->d_q, h->d_out, nullptr);
+    if (r != WXB_OK) return r;
+    CU(cudaMemcpyAsync(dq_host, h->d_out, bytes, cudaMemcpyDeviceToHost, 0));
+    CU(cudaStreamSynchronize(0));
+    return WXB_OK;
+}
+
+int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, const double* rhs0_host, double dt,
+                 double eps, int mode, double* out_host) {
+    if (!h) return WXB_EINVAL;
+    if (!q_host || !v_host || !rhs0_host || !out_host) {
+        set_err(h, "null host pointer");
+        return WXB_EINVAL;
+    }
+    int r = host_stage(h);
+    if (r != WXB_OK) return r;
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    CU(cudaMemcpyAsync(h->d_q, q_host, bytes, cudaMemcpyHostToDevice, 0));
+    CU(cudaMemcpyAsync(h->d_v, v_host, bytes, cudaMemcpyHostToDevice, 0));
+    CU(cudaMemcpyAsync(h->d_r0, rhs0_host, bytes, cudaMemcpyHostToDevice, 0));
+    r = wxb_jvp(h, h->d_q, h->d_v, h->d_r0, dt, eps, mode, h->d_out, nullptr);
+    if (r != WXB_OK) return r;
+    CU(cudaMemcpyAsync(out_host, h->d_out, bytes, cudaMemcpyDeviceToHost, 0));
+    CU(cudaStreamSynchronize(0));
+    return WXB_OK;
+}
+
+int wxb_timings(wxb_handle* h, float out_ms[3]) {
+    if (!h || !out_ms) return WXB_EINVAL;
+    if (!h->timed) {
+        set_err(h, "no completed evaluation to time");
+        return WXB_ESTATE;
+    }
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventSynchronize(h->ev[2]));
+    CU(cudaEventElapsedTime(&out_ms[0], h->ev[0], h->ev[1]));
+    CU(cudaEventElapsedTime(&out_ms[1], h->ev[1], h->ev[2]));
+    CU(cudaEventElapsedTime(&out_ms[2], h->ev[0], h->ev[2]));
+    return WXB_OK;
+}
+
+}  // extern "C"

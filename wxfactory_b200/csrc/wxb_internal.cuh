@@ -1,0 +1,113 @@
+// Internal declarations shared by the kernels and the C ABI (not part of the public interface).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/wxb200.h"
+
+// wx_factory/common/definitions.py:5-12
+#define WXB_P0 100000.0
+#define WXB_RD 287.05
+#define WXB_CPD 1005.46
+#define WXB_CVD (WXB_CPD - WXB_RD)
+#define WXB_GRAVITY 9.80616
+#define WXB_GAMMA (WXB_CPD / WXB_CVD)
+
+struct SlabTab {
+    int nslabs;
+    int ny[WXB_MAX_SLABS];
+    int ebase[WXB_MAX_SLABS + 1];     // first local element of each slab
+    int cbase[WXB_MAX_SLABS + 1];     // first local column of each slab
+    long long fmi[WXB_MAX_SLABS];     // offset (doubles) of the slab's block in fm_i / fm_j / fm_k
+    long long fmj[WXB_MAX_SLABS];
+    long long fmk[WXB_MAX_SLABS];
+};
+
+// Arguments of one evaluation (passed by value to every kernel).
+struct EvalArgs {
+    const double* q;      // state
+    const double* v;      // perturbation direction or nullptr
+    double eps;           // q + eps*v
+    const double* rhs0;   // cached base RHS (JVP modes)
+    double dt;
+    int mode;             // -1 plain RHS, WXB_JVP_FD, WXB_JVP_RAT
+    double* out;
+    double* trace;        // [num_var][faces][E][F] then ghost records [rec][num_var][nz][F]
+    double* sendbuf;
+    const double* sqrtg;
+    const double* h;
+    const double* chris;
+    const double* idz;
+    const double* damp;
+    const double* topo;
+    const double* fmi;
+    const double* fmj;
+    const double* fmk;
+    const double* topo_itf;
+    const int4* nbr;
+    const double* xform;
+    const int* send;
+    const double* ops;    // ext_w[n] ext_e[n] diff[n*n] corr[2n] hfilt[n*n]
+    const int* elist;     // optional list of elements to process (nullptr = all)
+    int nelist;
+    int E, C, nz, nx, nsend;
+    int has_damp, has_topo;
+    double tau0;
+    SlabTab st;
+};
+
+struct wxb_handle {
+    wxb_config cfg;
+    int device;
+    int n, P, F, nvar, nfaces;
+    int E, C;
+    SlabTab st;
+    // device arrays
+    double *d_ops, *d_sqrtg, *d_h, *d_chris, *d_idz, *d_damp, *d_topo, *d_fmi, *d_fmj, *d_fmk, *d_topo_itf, *d_xform;
+    int4* d_nbr;
+    int *d_send, *d_elist_inner, *d_elist_outer;
+    int n_inner, n_outer;
+    double *d_trace, *d_sendbuf;
+    int64_t trace_local;  // doubles in the local part of the trace array
+    // staging for the *_host entry points
+    double *d_q, *d_v, *d_r0, *d_out;
+    cudaEvent_t ev[3];
+    bool timed;
+    bool traces_done;
+    char err[512];
+};
+
+// launchers implemented per equation set
+int wxb_euler_traces(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_euler_main(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_sw_main(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_pack(const EvalArgs& a, int nvar, int F, cudaStream_t s);
+
+// decode a local element index into (slab, level k, local row jl, col i)
+struct ElemPos {
+    int s, k, jl, i, c;       // c = local column
+    long long qoff;           // offset of (var 0, this element, node 0) in the state
+    long long vstride;        // distance between variables in the state
+    int ny;
+};
+
+__device__ __forceinline__ ElemPos decode_elem(const SlabTab& st, int e, int nz, int nx, int P, int nvar) {
+    ElemPos r;
+    int s = 0;
+#pragma unroll
+    for (int t = 1; t < WXB_MAX_SLABS; ++t)
+        if (t < st.nslabs && e >= st.ebase[t]) s = t;
+    const int ny = st.ny[s];
+    const int el = e - st.ebase[s];
+    r.s = s;
+    r.ny = ny;
+    r.i = el % nx;
+    const int t2 = el / nx;
+    r.jl = t2 % ny;
+    r.k = t2 / ny;
+    r.c = st.cbase[s] + r.jl * nx + r.i;
+    r.vstride = (long long)nz * ny * nx * P;
+    r.qoff = (long long)nvar * P * st.ebase[s] + (long long)el * P;
+    return r;
+}

@@ -1,0 +1,324 @@
+"""Host-side mirror of the reference's RHS objects for the cubed sphere, backed by libwxb200.so.
+
+Drop-in surface (same names, argument meaning and error behaviour as the reference):
+
+* ``RhsB200.__call__(q) -> dq/dt`` / ``.full(q)``: ``RHS.__call__`` (wx_factory/rhs/rhs.py:75-125) and
+  ``RhsShallowWater.__call__`` (wx_factory/rhs/rhs_sw.py:38-56).  ``q`` may have any shape of the right size
+  (Krylov solvers pass flattened vectors, wx_factory/solvers/matvec.py:65); the result comes back in the
+  caller's shape as a fresh array the caller owns.
+* ``.timings / .retrieve_last_times() / .clear_timings() / .print_times()``: wx_factory/rhs/rhs.py:68-73,190-213.
+* ``matvec_fun(vec, dt, Q, rhs, rhs_handle, method)`` and ``matvec_rat`` / ``MatvecOpRat`` with the reference's
+  positional signatures (wx_factory/solvers/matvec.py:36-88); when ``rhs_handle`` is a ``RhsB200`` the fused
+  device JVP is used, otherwise the generic formula.
+* ``RhsBundleB200``: ``RhsBundle`` (wx_factory/rhs/rhs_selector.py:18-84) built from the reference's own
+  geometry / operators / metric objects.
+
+Arrays: numpy ``float64`` in -> numpy out (host path: H2D, kernels, D2H inside the call: what an unmodified
+reference integrator sees); anything exporting ``__dlpack__`` on the CUDA device (e.g. a torch tensor) in ->
+torch CUDA tensor out (device-resident path).  complex128 input (the reference's complex-step JVP) raises
+``TypeError``: this path implements the finite-difference JVP only (BASELINE.json north_star).
+"""
+
+import ctypes
+import math
+
+import numpy
+
+from . import capi
+from .layout import local_state, local_static
+from .partition import build_partition
+
+EPS_FD = math.sqrt(numpy.finfo(numpy.float32).eps)  # wx_factory/solvers/matvec.py:64
+
+
+class _DevPtr:
+    """Expose a raw device pointer through __cuda_array_interface__ so torch can view it (no copy)."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {
+            "shape": (int(count),),
+            "typestr": "<f8",
+            "data": (int(ptr), False),
+            "version": 3,
+            "strides": None,
+        }
+
+
+class RhsB200:
+    """dQ/dt = RHS(Q) on the cubed sphere for one rank of a 1/2/4/8-way partition."""
+
+    def __init__(self, problem, nranks=1, rank=0, device=0, process_group=None):
+        self.prob = problem
+        self.nranks, self.rank = int(nranks), int(rank)
+        self.device_index = int(device)
+        self.group = process_group
+        euler = problem.equations == "euler"
+        self.num_var = problem.num_var
+        nz = problem.nz if euler else 1
+        self.part = build_partition(
+            problem.nh,
+            nz,
+            problem.n,
+            problem.bnd_sn,
+            problem.bnd_we,
+            nranks=self.nranks,
+            rank=self.rank,
+            num_var=self.num_var,
+            nfaces=6 if euler else 4,
+        )
+        self._lib = capi.load()
+        cfg = capi.WxbConfig()
+        cfg.equations = capi.EQ_EULER3D if euler else capi.EQ_SW
+        cfg.n, cfg.nz, cfg.nx = problem.n, nz, problem.nh
+        cfg.nslabs = len(self.part.slabs)
+        if cfg.nslabs > capi.WXB_MAX_SLABS:
+            raise ValueError(f"too many slabs ({cfg.nslabs})")
+        for s, sl in enumerate(self.part.slabs):
+            cfg.slab_ny[s] = sl.ny
+        cfg.nghost, cfg.nsend = self.part.nghost, self.part.nsend
+        cfg.nxform = int(self.part.xform.shape[0])
+        cfg.advection_only = int(bool(getattr(problem, "advection_only", False)))
+        cfg.has_damping = int(euler and problem.damp is not None)
+        cfg.has_topo = int((not euler) and problem.hsurf is not None)
+        cfg.damp_tau0 = float(getattr(problem, "damp_tau0", 25.0))
+        self._static = local_static(problem, self.part)  # keep alive during create
+        arrs = capi.WxbStaticArrays()
+        for name, typ in capi._ARRAY_FIELDS:
+            a = self._static.get(name)
+            setattr(arrs, name, capi.ptr(a, typ) if a is not None and a.size else typ())
+        h = ctypes.c_void_p()
+        code = self._lib.wxb_create(ctypes.byref(cfg), ctypes.byref(arrs), self.device_index, ctypes.byref(h))
+        capi.check(self._lib, None, code, "wxb_create")
+        self._h = h
+        self._static = None
+        self.size = int(self._lib.wxb_state_size(self._h))
+        self.timestamps = []
+        self.timings = []
+        self._have_timing = False
+        self.launches = 0  # kernels launched by this object (bench.py's gpu_launches)
+        self._torch = None
+        self._send_t = self._recv_t = None
+        self._comm_stream = None
+
+    # ---- lifetime ---------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.wxb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    # ---- helpers ----------------------------------------------------------------------------------
+    @property
+    def shape(self):
+        return (self.size,)
+
+    def local_state(self, Qglobal):
+        """Extract this rank's flat state from a (6, num_var, ...) global array."""
+        return local_state(self.prob, self.part, Qglobal)
+
+    def _check(self, code, what):
+        capi.check(self._lib, self._h, code, what)
+
+    def _kernels_per_eval(self):
+        adv = self.prob.equations == "euler" and self.prob.advection_only
+        if adv:
+            return 0
+        return 2 + (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
+
+    def _tm(self):
+        if self._torch is None:
+            import torch
+
+            if not torch.cuda.is_available():
+                raise RuntimeError("wxfactory_b200 needs a CUDA device: there is no CPU fallback")
+            self._torch = torch
+        return self._torch
+
+    def _as_device(self, x, name):
+        """Return (flat contiguous float64 CUDA tensor, original shape) of a device array-like."""
+        torch = self._tm()
+        if not isinstance(x, torch.Tensor):
+            x = torch.from_dlpack(x)
+        if x.is_complex():
+            raise TypeError("complex state: the B200 path implements the finite-difference JVP only (jacobian_method = fd)")
+        if x.dtype != torch.float64:
+            raise TypeError(f"{name} must be float64, got {x.dtype}")
+        if not x.is_cuda or x.device.index != self.device_index:
+            raise ValueError(f"{name} must live on cuda:{self.device_index}")
+        if x.numel() != self.size:
+            raise ValueError(f"{name} has {x.numel()} values, this RHS expects {self.size}")
+        return x.contiguous().view(-1), tuple(x.shape)
+
+    def _as_host(self, x, name):
+        if numpy.iscomplexobj(x):
+            raise TypeError("complex state: the B200 path implements the finite-difference JVP only (jacobian_method = fd)")
+        a = numpy.ascontiguousarray(x, dtype=numpy.float64)
+        if a.size != self.size:
+            raise ValueError(f"{name} has {a.size} values, this RHS expects {self.size}")
+        return a
+
+    # ---- halo exchange between ranks (NCCL through torch.distributed) -------------------------------
+    def _exchange(self, stream):
+        torch = self._tm()
+        import torch.distributed as dist
+
+        if self._send_t is None:
+            ns, nr = int(self._lib.wxb_send_size(self._h)), int(self._lib.wxb_recv_size(self._h))
+            self._send_t = torch.as_tensor(_DevPtr(self._lib.wxb_send_buffer(self._h), ns), device=f"cuda:{self.device_index}")
+            self._recv_t = torch.as_tensor(_DevPtr(self._lib.wxb_recv_buffer(self._h), nr), device=f"cuda:{self.device_index}")
+            euler = self.prob.equations == "euler"
+            self._rec = self.num_var * (self.prob.nz if euler else 1) * self.prob.F
+        ops = []
+        for peer, first, cnt in self.part.send_peers:
+            ops.append(dist.P2POp(dist.isend, self._send_t[first * self._rec : (first + cnt) * self._rec], peer, group=self.group))
+        for peer, first, cnt in self.part.recv_peers:
+            ops.append(dist.P2POp(dist.irecv, self._recv_t[first * self._rec : (first + cnt) * self._rec], peer, group=self.group))
+        with torch.cuda.stream(stream):
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+    # ---- evaluation -------------------------------------------------------------------------------
+    def _eval_device(self, q, v, rhs0, dt, eps, mode):
+        torch = self._tm()
+        out = torch.empty(self.size, dtype=torch.float64, device=q.device)
+        stream = torch.cuda.current_stream(q.device)
+        sp = ctypes.c_void_p(stream.cuda_stream)
+        vp = ctypes.c_void_p(v.data_ptr()) if v is not None else None
+        rp = ctypes.c_void_p(rhs0.data_ptr()) if rhs0 is not None else None
+        if self.part.nghost == 0 and self.part.nsend == 0:
+            if mode < 0:
+                self._check(self._lib.wxb_rhs(self._h, q.data_ptr(), out.data_ptr(), sp), "wxb_rhs")
+            else:
+                self._check(self._lib.wxb_jvp(self._h, q.data_ptr(), vp, rp, dt, eps, mode, out.data_ptr(), sp), "wxb_jvp")
+        else:
+            if self._comm_stream is None:
+                self._comm_stream = torch.cuda.Stream(device=q.device)
+            self._check(self._lib.wxb_traces(self._h, q.data_ptr(), vp, eps, sp), "wxb_traces")
+            cs = self._comm_stream
+            cs.wait_stream(stream)
+            self._exchange(cs)  # overlaps with the inner elements below
+            self._check(self._lib.wxb_finish(self._h, q.data_ptr(), vp, rp, dt, eps, mode, 1, out.data_ptr(), sp), "wxb_finish")
+            stream.wait_stream(cs)
+            self._check(self._lib.wxb_finish(self._h, q.data_ptr(), vp, rp, dt, eps, mode, 2, out.data_ptr(), sp), "wxb_finish")
+        self.launches += self._kernels_per_eval()
+        self._have_timing = True
+        return out
+
+    def __call__(self, q):
+        if len(self.timestamps) > 0:
+            self.retrieve_last_times()
+        if isinstance(q, numpy.ndarray):
+            if self.nranks != 1:
+                raise ValueError("host (numpy) states are supported on a single rank only; pass device tensors")
+            a = self._as_host(q, "q")
+            out = numpy.empty_like(a)
+            self._check(self._lib.wxb_rhs_host(self._h, a.ctypes.data, out.ctypes.data), "wxb_rhs_host")
+            self.launches += self._kernels_per_eval()
+            self._have_timing = True
+            self.timestamps = [True]
+            return out.reshape(q.shape)
+        qd, shape = self._as_device(q, "q")
+        out = self._eval_device(qd, None, None, 0.0, 0.0, -1)
+        self.timestamps = [True]
+        return out.view(shape)
+
+    def full(self, q):
+        return self.__call__(q)
+
+    def jvp(self, vec, dt, Q, rhs0, mode="fd", eps=EPS_FD):
+        """Fused FD Jacobian-vector product: dt*(RHS(Q+eps*vec)-rhs0)/eps ('fd') or vec - 0.5*that ('rat').
+        Returns a flattened array like the reference's matvec_fun / matvec_rat."""
+        m = {"fd": capi.JVP_FD, "rat": capi.JVP_RAT}.get(mode)
+        if m is None:
+            raise ValueError(f"unknown JVP mode {mode!r} (complex-step is not available on this path)")
+        if isinstance(Q, numpy.ndarray):
+            if self.nranks != 1:
+                raise ValueError("host (numpy) states are supported on a single rank only; pass device tensors")
+            q, v, r = self._as_host(Q, "Q"), self._as_host(vec, "vec"), self._as_host(rhs0, "rhs")
+            out = numpy.empty_like(q)
+            self._check(
+                self._lib.wxb_jvp_host(self._h, q.ctypes.data, v.ctypes.data, r.ctypes.data, float(dt), float(eps), m, out.ctypes.data),
+                "wxb_jvp_host",
+            )
+            self.launches += self._kernels_per_eval()
+            return out.reshape(-1)
+        q, _ = self._as_device(Q, "Q")
+        v, _ = self._as_device(vec, "vec")
+        r, _ = self._as_device(rhs0, "rhs")
+        return self._eval_device(q, v, r, float(dt), float(eps), m)
+
+    # ---- timing vocabulary of the reference (rhs.py:68-73,190-213) ---------------------------------
+    def clear_timings(self):
+        self.timestamps = []
+        self.timings = []
+
+    def retrieve_last_times(self):
+        if not self._have_timing:
+            return
+        ms = (ctypes.c_float * 3)()
+        if self._lib.wxb_timings(self._h, ctypes.byref(ms)) == 0:
+            self.timings.append([ms[0] * 1e-3, ms[1] * 1e-3, ms[2] * 1e-3])
+
+    def print_times(self):
+        if not self.timings:
+            return
+        t = numpy.array(self.timings) * 1000.0
+        print(
+            f"RHS times (device):\n  Traces (extrapolation+pack): {t[:, 0].mean():7.3f} ms\n"
+            f"  Main (flux, Riemann, lift, forcing): {t[:, 1].mean():7.3f} ms\n  Total: {t[:, 2].mean():7.3f} ms"
+        )
+
+
+def matvec_fun(vec, dt, Q, rhs, rhs_handle, method="fd"):
+    """wx_factory/solvers/matvec.py:36-68 with the same positional signature (FD only)."""
+    if method == "complex":
+        raise TypeError("complex-step JVP is not available on the B200 path: set jacobian_method = fd")
+    owner = getattr(rhs_handle, "__self__", rhs_handle)
+    if isinstance(owner, RhsB200):
+        return owner.jvp(vec, dt, Q, rhs, mode="fd")
+    Qvec = Q + EPS_FD * vec.reshape(Q.shape)
+    jac = dt * (rhs_handle(Qvec) - rhs) / EPS_FD
+    return jac.flatten()
+
+
+def matvec_rat(vec, dt, Q, rhs, rhs_handle):
+    """wx_factory/solvers/matvec.py:76-88."""
+    owner = getattr(rhs_handle, "__self__", rhs_handle)
+    if isinstance(owner, RhsB200):
+        return owner.jvp(vec, dt, Q, rhs, mode="rat")
+    Qvec = Q + EPS_FD * vec.reshape(Q.shape)
+    jac = dt * (rhs_handle(Qvec) - rhs) / EPS_FD
+    return vec - 0.5 * jac.flatten()
+
+
+class MatvecOpRat:
+    """wx_factory/solvers/matvec.py:71-73."""
+
+    def __init__(self, dt, Q, rhs_vec, rhs_handle):
+        self.dt, self.Q, self.rhs_vec, self.rhs_handle = dt, Q, rhs_vec, rhs_handle
+        self.dtype, self.shape = Q.dtype, tuple(Q.shape)
+        self.size = int(numpy.prod(self.shape))
+
+    def __call__(self, vec):
+        return matvec_rat(vec, self.dt, self.Q, self.rhs_vec, self.rhs_handle)
+
+
+class RhsBundleB200:
+    """wx_factory/rhs/rhs_selector.py:18-84: ``.full`` is the RHS callable handed to every integrator
+    (wx_factory/simulation/simulation.py:336-395).  ``ranks`` = the 6 per-panel reference objects
+    (geom, ops, metric, config[, topo]); see from_reference.py."""
+
+    def __init__(self, ranks, device=0):
+        from .from_reference import problem_from_reference
+
+        eq = str(ranks[0].config.equations).lower()
+        if eq not in ("euler", "shallow_water"):
+            raise ValueError(f"Unrecognized combination of equations ({eq}) and geometry")
+        self.problem = problem_from_reference(ranks)
+        self.full = RhsB200(self.problem, device=device)
+        self.shape = self.problem.state_shape
