@@ -1,0 +1,498 @@
+#!/usr/bin/env python
+"""Throughput benchmark of the B200 cubed-sphere DG right-hand side + fused FD Jacobian-vector product.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Metric (BASELINE.json): FP64 DOF-updates/s.  One *step* = one RHS evaluation dQ/dt = RHS(Q) followed by one fused
+finite-difference Jacobian-vector product J(Q) v around it (what an EPI/KIOPS or Rosenbrock/FGMRES integrator does per
+Krylov vector), i.e. 2 x (5 x nodes) DOF-updates.  Workload = BASELINE.json configs[4], the synthetic
+high-resolution Euler state (n = 4, 12 x nh x nh elements per panel, nh = 48 at one GPU and ~48*sqrt(N) at N so
+that the elements per GPU stay fixed: weak scaling): metric, operators and state of a reference-built DCMIP 3-1
+problem tiled along the element axes (wxfactory_b200/synthetic.py).  The four .ini configs of BASELINE.json hold
+16 k .. 146 k DOFs -- microseconds of HBM time, launch-bound -- and are parity-test cases, not bench lines.
+
+JSON line keys (one line, rank 0): the base contract's, plus
+  roofline      algorithmic HBM bytes of one RHS evaluation (B_rhs(n) = 360 + 96/n bytes per node) over the
+                evaluation's device time (both kernels of the evaluation: traces + main), measured with the C
+                ABI's own CUDA events on the launching stream for every RHS launch of the timed region;
+                roofline_jvp is the same for the JVP launches (B_jvp(n) = 440 + 96/n).
+  e2e           the same step through the public API with HOST numpy arrays (pinned): H2D of every input and D2H
+                of every result inside the timed region.
+  cpu_baseline  the numpy oracle (bit-identical restatement of the reference's numpy RHS) on a bounded sample of the
+                same workload (same tiling at 8 x 8 x 8 elements per panel), one single-threaded replica per core.
+  parity        full-size check of the device result against the oracle through the tiling periodicity property.
+
+`--impl reference` times only the CPU arm (rank 0; other ranks exit) and prints the same line with "impl": "reference".
+"""
+
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASE_FIXTURE = os.path.join(ROOT, "tests", "golden", "dcmip31_n4.npz")
+METRIC = "DG RHS+JVP DOF-updates/s FP64"
+UNIT = "DOF-updates/s"
+SMALL_NZ, SMALL_NH = 8, 8  # the oracle-sized twin of the workload (2 x the base block per axis)
+L2_BYTES = 126 * 2**20
+
+
+def nh_for(ngpus, nh1):
+    """Elements per panel side that keep 6*nh^2/N (elements per GPU) ~fixed and 6*nh divisible by N."""
+    nh = nh1 * math.sqrt(ngpus)
+    step = 4
+    cands = [int(round(nh / step)) * step + d for d in (-4, 0, 4)]
+    cands = [c for c in cands if c > 0 and (6 * c) % ngpus == 0]
+    return min(cands, key=lambda c: abs(c - nh))
+
+
+def b_rhs(n):
+    return 360.0 + 96.0 / n  # bytes per node per RHS evaluation
+
+
+def b_jvp(n):
+    return 440.0 + 96.0 / n  # + v and the cached base RHS
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU arm: the numpy oracle on the small twin, one single-threaded replica per core (spawned before CUDA exists)
+_W = {}
+
+
+def _cpu_init():
+    import numpy
+
+    from oracle import jvp_oracle
+    from wxfactory_b200 import synthetic as syn
+    from wxfactory_b200.problem import load_problem
+
+    numpy.seterr(all="ignore")
+    base, ex = load_problem(BASE_FIXTURE)
+    Qb = syn.base_state(ex["Q0"])
+    vb = syn.base_direction(Qb)
+    small = syn.TiledEulerProblem(base, SMALL_NZ, SMALL_NH)
+    _W["orc"] = jvp_oracle.make_oracle(small.materialize())
+    _W["Q"] = small.global_state(Qb)
+    _W["v"] = small.global_state(vb).ravel()
+    _W["dt"] = float(ex["dt"])
+    _W["jvp"] = jvp_oracle.matvec_fd
+
+
+def _cpu_step(_):
+    t = time.perf_counter()
+    r0 = _W["orc"].rhs(_W["Q"])
+    _W["jvp"](_W["orc"].rhs, _W["v"], _W["dt"], _W["Q"], r0)
+    return time.perf_counter() - t
+
+
+def cpu_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_cpu_arm(steps, warmup, max_workers=64):
+    """Returns dict(value, ms_per_step, cores, sample, dofs)."""
+    import multiprocessing as mp
+
+    workers = max(1, min(cpu_cores(), max_workers))
+    saved = {k: os.environ.get(k) for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")}
+    for k in saved:
+        os.environ[k] = "1"
+    try:
+        ctx = mp.get_context("spawn")
+        with ctx.Pool(workers, initializer=_cpu_init) as pool:
+            for _ in range(max(1, warmup)):
+                pool.map(_cpu_step, range(workers), chunksize=1)
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                pool.map(_cpu_step, range(workers), chunksize=1)
+            dt = time.perf_counter() - t0
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    dofs = 5 * 6 * SMALL_NZ * SMALL_NH * SMALL_NH * 64
+    return {
+        "value": workers * 2 * dofs * steps / dt,
+        "ms_per_step": 1e3 * dt / steps,
+        "cores": workers,
+        "dofs": dofs,
+        "sample": (
+            f"{workers} single-threaded replicas of the numpy oracle, each {steps} steps (RHS + FD-JVP) on the same "
+            f"tiled workload at {SMALL_NZ}x{SMALL_NH}x{SMALL_NH} elements/panel (n=4, {dofs} DOFs)"
+        ),
+    }
+
+
+# ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples while a timed region runs (B200_PROFILING.md recipe)."""
+
+    FIELDS = (
+        "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    )
+
+    def __init__(self, gpus):
+        self.gpus = set(gpus)
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE,
+                stderr=subprocess.DEVNULL,
+                text=True,
+            )
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self, windows):
+        """windows: list of (t0, t1) perf_counter intervals that were timed."""
+        sm, smax, reasons, power = [], 0.0, set(), 0.0
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if not any(a <= t <= b for a, b in windows):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                if int(f[0]) not in self.gpus:
+                    continue
+                sm.append(float(f[1]))
+                smax = max(smax, float(f[2]))
+                power = max(power, float(f[3]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {
+            "sm_mhz": statistics.median(sm) if sm else None,
+            "sm_max_mhz": smax or None,
+            "reasons": sorted(reasons),
+            "samples": len(sm),
+            "power_w_max": power or None,
+        }
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import numpy
+    import torch
+    import torch.distributed as dist
+
+    from wxfactory_b200 import EPS_FD, RhsB200
+    from wxfactory_b200 import synthetic as syn
+    from wxfactory_b200.problem import load_problem
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the B200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- workload -----------------------------------------------------------------------------------------
+    base, ex = load_problem(BASE_FIXTURE)
+    n = base.n
+    nz = args.nz
+    nh = args.nh if args.nh > 0 else nh_for(world, args.nh1)
+    tiled = syn.TiledEulerProblem(base, nz, nh)
+    Qb = syn.base_state(ex["Q0"])
+    vb = syn.base_direction(Qb)
+    dt = float(ex["dt"])
+    t_setup = time.perf_counter()
+    rhs = RhsB200(tiled, nranks=world, rank=rank, device=local_rank)
+    size = rhs.size
+    nodes_local = size // 5
+    # host copies live in pinned memory: they are what the reference's integrators would hold
+    pin = lambda: torch.empty(size, dtype=torch.float64, pin_memory=True)  # noqa: E731
+    q_h, v_h, r0_h = pin(), pin(), pin()
+    q_h.numpy()[:] = rhs.local_state(Qb)
+    v_h.numpy()[:] = rhs.local_state(vb)
+    q_d, v_d = q_h.to(dev), v_h.to(dev)
+    t_setup = time.perf_counter() - t_setup
+    total_nodes = tiled.num_nodes
+    total_dofs = tiled.num_dofs
+    state_bytes = size * 8
+
+    # ---- full-size parity through the tiling periodicity property (untimed) ---------------------------------
+    parity = None
+    rhs0_d = rhs(q_d)
+    jv_d = rhs.jvp(v_d, dt, q_d, rhs0_d, mode="fd")
+    torch.cuda.synchronize()
+    if not args.skip_check:
+        from oracle import jvp_oracle
+
+        small = syn.TiledEulerProblem(base, SMALL_NZ, SMALL_NH)
+        orc = jvp_oracle.make_oracle(small.materialize())
+        Qs, vs = small.global_state(Qb), small.global_state(vb)
+        with numpy.errstate(all="ignore"):
+            want_r = orc.rhs(Qs)
+            want_j = jvp_oracle.matvec_fd(orc.rhs, vs.ravel(), dt, Qs, want_r).reshape(Qs.shape)
+        e_r, cnt = syn.check_against_small(tiled, rhs.part, rhs0_d, want_r)
+        e_j, _ = syn.check_against_small(tiled, rhs.part, jv_d, want_j)
+        # the FD formula amplifies RHS rounding by dt/eps: state the JVP error relative to dt*|rhs|/eps
+        jscale = dt * float(numpy.linalg.norm(want_r)) / EPS_FD / max(float(numpy.linalg.norm(want_j)), 1e-300)
+        e_j_scaled = e_j / jscale
+        e_r, e_j_scaled, cnt = max_over_ranks(e_r), max_over_ranks(e_j_scaled), int(max_over_ranks(float(cnt)))
+        parity = {
+            "rhs_rel_err": e_r,
+            "jvp_err_over_dt_rhs_eps": e_j_scaled,
+            "elements_checked_per_rank": cnt,
+            "tolerance": 1e-12,
+            "ok": bool(e_r <= 1e-12 and e_j_scaled <= 1e-12),
+            "how": "every element off the panel edges / bottom / top vs the numpy oracle on the 8x8x8 twin (tiling periodicity)",
+        }
+        del orc, Qs, vs, want_r, want_j
+    r0_h.copy_(rhs0_d)
+    torch.cuda.synchronize()
+
+    def step_device():
+        out = rhs(q_d)
+        return rhs.jvp(v_d, dt, q_d, out, mode="fd")
+
+    def step_host():
+        out = rhs(q_h.numpy())
+        return rhs.jvp(v_h.numpy(), dt, q_h.numpy(), out, mode="fd")
+
+    sampler = ClockSampler(range(world)) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+
+    # ---- device-resident timed region -----------------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    launches0 = rhs.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    w1 = time.perf_counter()
+    launches = rhs.launches - launches0
+    ms_dev = max_over_ranks(e0.elapsed_time(e1))
+    hist, modes = rhs.timing_history(min(256, 2 * args.steps))
+    t_rhs = hist[modes < 0]
+    t_jvp = hist[modes >= 0]
+
+    # ---- end to end through the public API with host arrays ------------------------------------------------
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    for _ in range(2):
+        step_host()
+    barrier()
+    w2 = time.perf_counter()
+    e0.record()
+    for _ in range(e2e_steps):
+        step_host()
+    e1.record()
+    barrier()
+    w3 = time.perf_counter()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    if sampler:
+        time.sleep(0.2)
+        sampler.stop()
+
+    peak, peak_src = measured_peaks()
+    line = None
+    if rank == 0:
+        def roof(tt, bytes_per_node, what):
+            if len(tt) == 0:
+                return None
+            sec = float(tt[:, 2].mean()) * 1e-3
+            ach = bytes_per_node * nodes_local / sec / 1e9
+            return {
+                "bound": "hbm",
+                "achieved": ach,
+                "peak": peak,
+                "unit": "GB/s",
+                "frac": ach / peak,
+                "traffic": None,
+                "kernels": ["euler_traces<4>", "euler_main<4>"],
+                "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
+                "algorithmic_bytes_per_node": bytes_per_node,
+                "nodes_per_launch": nodes_local,
+                "launches_timed": int(len(tt)),
+                "peak_source": peak_src,
+                "what": what,
+            }
+
+        clocks = sampler.summary([(w0 - 0.15, w1 + 0.15), (w2, w3)]) if sampler else None
+        line = {
+            "metric": METRIC,
+            "value": 2.0 * total_dofs * args.steps / (ms_dev * 1e-3),
+            "unit": UNIT,
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": args.warmup,
+            "ms_per_step": ms_dev / args.steps,
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": None,
+            "dtype": "f64",
+            "data": "synthetic (reference-built DCMIP 3-1 n=4 metric/state tiled along the element axes)",
+            "config": {
+                "workload": f"configs[4] synthetic cubed-sphere Euler: n=4, {nz}x{nh}x{nh} elements/panel x 6 panels",
+                "num_solpts": n,
+                "elements_per_panel": [nz, nh, nh],
+                "nodes": total_nodes,
+                "dofs": total_dofs,
+                "step": "1 RHS + 1 fused FD-JVP = 2 x dofs DOF-updates",
+                "partition": f"{world} rank(s), contiguous rows of element columns; face-trace halo over NCCL p2p",
+                "l2": f"state {state_bytes / 2**20:.0f} MiB + metric {nodes_local * 35 * 8 / 2**20:.0f} MiB per GPU > L2 ({L2_BYTES >> 20} MiB): no flush needed",
+            },
+            "e2e": {
+                "value": 2.0 * total_dofs * e2e_steps / (ms_e2e * 1e-3),
+                "unit": UNIT,
+                "h2d_bytes_per_step": 4 * state_bytes,
+                "d2h_bytes_per_step": 2 * state_bytes,
+                "steps": e2e_steps,
+                "ms_per_step": ms_e2e / e2e_steps,
+                "how": "RhsB200.__call__(numpy) + RhsB200.jvp(numpy...) -> wxb_rhs_host / wxb_jvp_host: pinned host arrays in, numpy out",
+            },
+            "gpu_launches": int(launches),
+            "roofline": roof(t_rhs, b_rhs(n), "one RHS evaluation"),
+            "roofline_jvp": roof(t_jvp, b_jvp(n), "one fused FD-JVP evaluation (cached base RHS)"),
+            "clocks": clocks,
+            "parity": parity,
+            "setup_s": t_setup,
+        }
+    rhs.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return line
+
+
+def reference_line(args):
+    """`--impl reference`: the CPU arm alone, on the arm's own config/metric/unit."""
+    nh = args.nh if args.nh > 0 else nh_for(args.gpus, args.nh1)
+    cpu = run_cpu_arm(args.steps, args.warmup)
+    return {
+        "impl": "reference",
+        "metric": METRIC,
+        "value": cpu["value"],
+        "unit": UNIT,
+        "n_gpus": args.gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": cpu["ms_per_step"],
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "f64",
+        "data": "synthetic (reference-built DCMIP 3-1 n=4 metric/state tiled along the element axes)",
+        "config": {
+            "workload": f"configs[4] synthetic cubed-sphere Euler: n=4, {args.nz}x{nh}x{nh} elements/panel x 6 panels",
+            "step": "1 RHS + 1 FD-JVP = 2 x dofs DOF-updates",
+            "note": "each step is a bounded sample of the workload (see cpu_baseline.sample); throughput is per DOF-update",
+        },
+        "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]},
+        "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--nz", type=int, default=12, help="elements per column")
+    ap.add_argument("--nh1", type=int, default=48, help="elements per panel side at one GPU (scaled by sqrt(N))")
+    ap.add_argument("--nh", type=int, default=0, help="override the elements per panel side")
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--cpu-steps", type=int, default=10)
+    ap.add_argument("--skip-check", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+
+    rank = int(os.environ.get("RANK", "0"))
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        print(json.dumps(reference_line(args)), flush=True)
+        return 0
+
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+
+    line = run_b200(args)
+    if rank == 0:
+        if args.gpus == 1 and not args.skip_cpu:
+            cpu = run_cpu_arm(args.cpu_steps, 2)
+            line["cpu_baseline"] = {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]}
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

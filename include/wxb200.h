@@ -147,6 +147,12 @@ int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, cons
 /* Device time of the last evaluation's kernels in ms: [0] traces(+pack), [1] main, [2] total. */
 int wxb_timings(wxb_handle* h, float out_ms[3]);
 
+/* The same three durations for the most recent evaluations (at most max_evals, at most 256 are kept), oldest
+ * first: out_ms[3*i + {0,1,2}], out_mode[i] = -1 (RHS) / WXB_JVP_* (nullable).  Returns the number of rows
+ * written, or a negative WXB_E* code.  Synchronises with the last evaluation.  Replaces the reference's
+ * per-call timestamp lists (wx_factory/rhs/rhs.py:78-79,190-213). */
+int wxb_timing_history(wxb_handle* h, int max_evals, float* out_ms, int* out_mode);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,10 +1,17 @@
 """Parity of the CUDA path (through the C ABI) with the reference's golden vectors and with the oracle.
 
 Tolerances (FP64, BASELINE.json north_star: 1e-12 relative per RHS evaluation):
-  RHS_TOL  relative L2 error of the whole RHS and of every variable, vs the reference's own output
+  RHS_TOL  relative L2 error of the whole RHS and of every variable, vs the reference's own output.  Where the
+           reference's own float64 result is further than that from the exactly-rounded evaluation of its formulas
+           (tests/golden/conditioning.json, made by oracle/refharness/conditioning.py with an 80-bit oracle: only
+           dcmip31_n4, a hydrostatic state at rest whose RHS is a 1e-10-relative residue of cancelling terms), the
+           bound is the reference's own rounding error: no other summation order can agree more closely.
   JVP_TOL  FD-JVP error relative to dt*|rhs|/eps (the FD formula amplifies RHS rounding by 1/eps ~ 2900,
            SURVEY 7.3), vs the reference's matvec_fun(..., 'fd') / matvec_rat outputs
 """
+
+import json
+import os
 
 import numpy
 import pytest
@@ -15,6 +22,16 @@ pytestmark = pytest.mark.gpu
 
 RHS_TOL = 1e-12
 JVP_TOL = 1e-12
+with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "conditioning.json")) as _f:
+    CONDITIONING = json.load(_f)["cases"]
+
+
+def rhs_tol(name):
+    return max(RHS_TOL, CONDITIONING[name]["ref_rounding"])
+
+
+def var_tol(name, v):
+    return max(10 * RHS_TOL, CONDITIONING[name]["ref_rounding_per_var"][v])
 
 
 def rel(a, b):
@@ -44,9 +61,9 @@ def test_rhs_matches_reference_host_path(rhs_cache, name):
     rhs, prob, ex = rhs_cache(name)
     out = rhs(ex["Q0"])
     assert isinstance(out, numpy.ndarray) and out.shape == ex["Q0"].shape
-    assert rel(out, ex["rhs0"]) <= RHS_TOL
+    assert rel(out, ex["rhs0"]) <= rhs_tol(name)
     for v in range(prob.num_var):
-        assert rel(out[:, v], ex["rhs0"][:, v]) <= RHS_TOL * 10, f"variable {v}"
+        assert rel(out[:, v], ex["rhs0"][:, v]) <= var_tol(name, v), f"variable {v}"
 
 
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
@@ -57,7 +74,7 @@ def test_rhs_matches_reference_device_path(rhs_cache, name):
     q = torch.from_numpy(ex["Q0"]).cuda()
     out = rhs(q.view(-1))  # flattened Krylov-style input keeps its shape
     assert out.shape == (q.numel(),) and out.is_cuda
-    assert rel(out.cpu().numpy().reshape(ex["rhs0"].shape), ex["rhs0"]) <= RHS_TOL
+    assert rel(out.cpu().numpy().reshape(ex["rhs0"].shape), ex["rhs0"]) <= rhs_tol(name)
     assert torch.equal(q, torch.from_numpy(ex["Q0"]).cuda()), "input must not be modified"
 
 
@@ -69,7 +86,7 @@ def test_jvp_matches_reference(rhs_cache, name):
 
     rhs, prob, ex = rhs_cache(name)
     dt = float(ex["dt"])
-    scale = dt * numpy.linalg.norm(ex["rhs0"]) / EPS_FD
+    scale = dt * numpy.linalg.norm(ex["rhs0"]) / EPS_FD * (rhs_tol(name) / RHS_TOL)
     # host arrays, the reference's positional signature
     fd = matvec_fun(ex["v"].ravel(), dt, ex["Q0"], ex["rhs0"], rhs.full, "fd")
     assert fd.shape == (ex["Q0"].size,)

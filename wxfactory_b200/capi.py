@@ -80,6 +80,7 @@ EXPORTS = [
     "wxb_rhs_host",
     "wxb_jvp_host",
     "wxb_timings",
+    "wxb_timing_history",
 ]
 
 _lib = None
@@ -117,6 +118,8 @@ def load():
     lib.wxb_rhs_host.argtypes = [vp, vp, vp]
     lib.wxb_jvp_host.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp]
     lib.wxb_timings.argtypes = [vp, ctypes.POINTER(ctypes.c_float * 3)]
+    lib.wxb_timing_history.argtypes = [vp, i32, vp, vp]
+    lib.wxb_timing_history.restype = i32
     _lib = lib
     return lib
 

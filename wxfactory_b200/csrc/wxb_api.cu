@@ -150,7 +150,9 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
         UP(h->d_elist_inner, inner.data(), inner.size());
         UP(h->d_elist_outer, outer.data(), outer.size());
     }
-    for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev[i]));
+    for (int r = 0; r < WXB_TIMING_RING; ++r)
+        for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev_ring[r][i]));
+    h->ev = h->ev_ring[0];
     return WXB_OK;
 }
 
@@ -217,6 +219,7 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
     }
     EvalArgs a;
     fill_args(h, a, q, v, nullptr, 0.0, eps, -1, nullptr);
+    h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     CU(cudaEventRecord(h->ev[0], s));
     int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
     if (r == 0) r = wxb_pack(a, h->nvar, h->F, s);
@@ -262,6 +265,8 @@ int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs
     }
     if (part != 1) {
         CU(cudaEventRecord(h->ev[2], s));
+        h->ev_mode[h->nevals % WXB_TIMING_RING] = mode;
+        h->nevals++;
         h->timed = true;
     }
     return WXB_OK;
@@ -334,8 +339,9 @@ int wxb_destroy(wxb_handle* h) {
                     h->d_r0,   h->d_out};
     for (void* p : ptrs)
         if (p) cudaFree(p);
-    for (int i = 0; i < 3; ++i)
-        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (int r = 0; r < WXB_TIMING_RING; ++r)
+        for (int i = 0; i < 3; ++i)
+            if (h->ev_ring[r][i]) cudaEventDestroy(h->ev_ring[r][i]);
     delete h;
     return WXB_OK;
 }
@@ -462,11 +468,29 @@ int wxb_timings(wxb_handle* h, float out_ms[3]) {
         return WXB_ESTATE;
     }
     CU(cudaSetDevice(h->device));
-    CU(cudaEventSynchronize(h->ev[2]));
-    CU(cudaEventElapsedTime(&out_ms[0], h->ev[0], h->ev[1]));
-    CU(cudaEventElapsedTime(&out_ms[1], h->ev[1], h->ev[2]));
-    CU(cudaEventElapsedTime(&out_ms[2], h->ev[0], h->ev[2]));
+    cudaEvent_t* ev = h->ev_ring[(h->nevals - 1) % WXB_TIMING_RING];
+    CU(cudaEventSynchronize(ev[2]));
+    CU(cudaEventElapsedTime(&out_ms[0], ev[0], ev[1]));
+    CU(cudaEventElapsedTime(&out_ms[1], ev[1], ev[2]));
+    CU(cudaEventElapsedTime(&out_ms[2], ev[0], ev[2]));
     return WXB_OK;
+}
+
+int wxb_timing_history(wxb_handle* h, int max_evals, float* out_ms, int* out_mode) {
+    if (!h || !out_ms || max_evals < 0) return WXB_EINVAL;
+    CU(cudaSetDevice(h->device));
+    long long n = h->nevals < max_evals ? h->nevals : max_evals;
+    if (n > WXB_TIMING_RING) n = WXB_TIMING_RING;
+    for (long long i = 0; i < n; ++i) {
+        const long long id = h->nevals - n + i;  // oldest first
+        cudaEvent_t* ev = h->ev_ring[id % WXB_TIMING_RING];
+        CU(cudaEventSynchronize(ev[2]));
+        CU(cudaEventElapsedTime(&out_ms[3 * i + 0], ev[0], ev[1]));
+        CU(cudaEventElapsedTime(&out_ms[3 * i + 1], ev[1], ev[2]));
+        CU(cudaEventElapsedTime(&out_ms[3 * i + 2], ev[0], ev[2]));
+        if (out_mode) out_mode[i] = h->ev_mode[id % WXB_TIMING_RING];
+    }
+    return (int)n;
 }
 
 }  // extern "C"

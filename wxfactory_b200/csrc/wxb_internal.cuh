@@ -13,6 +13,8 @@
 #define WXB_GRAVITY 9.80616
 #define WXB_GAMMA (WXB_CPD / WXB_CVD)
 
+#define WXB_TIMING_RING 256
+
 struct SlabTab {
     int nslabs;
     int ny[WXB_MAX_SLABS];
@@ -71,7 +73,11 @@ struct wxb_handle {
     int64_t trace_local;  // doubles in the local part of the trace array
     // staging for the *_host entry points
     double *d_q, *d_v, *d_r0, *d_out;
-    cudaEvent_t ev[3];
+    // one event triple per evaluation, in a ring: [0] start, [1] traces(+pack) done, [2] main done
+    cudaEvent_t ev_ring[WXB_TIMING_RING][3];
+    int ev_mode[WXB_TIMING_RING];
+    cudaEvent_t* ev;      // triple of the evaluation in flight
+    long long nevals;     // completed evaluations
     bool timed;
     bool traces_done;
     char err[512];

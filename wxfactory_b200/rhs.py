@@ -81,7 +81,8 @@ class RhsB200:
         cfg.has_damping = int(euler and problem.damp is not None)
         cfg.has_topo = int((not euler) and problem.hsurf is not None)
         cfg.damp_tau0 = float(getattr(problem, "damp_tau0", 25.0))
-        self._static = local_static(problem, self.part)  # keep alive during create
+        make_static = getattr(problem, "local_static", None)  # synthetic.TiledEulerProblem builds its slabs lazily
+        self._static = make_static(self.part) if make_static else local_static(problem, self.part)  # keep alive during create
         arrs = capi.WxbStaticArrays()
         for name, typ in capi._ARRAY_FIELDS:
             a = self._static.get(name)
@@ -118,7 +119,11 @@ class RhsB200:
         return (self.size,)
 
     def local_state(self, Qglobal):
-        """Extract this rank's flat state from a (6, num_var, ...) global array."""
+        """Extract this rank's flat state from a (6, num_var, ...) global array (for a tiled synthetic problem:
+        from the base block's state)."""
+        tiled = getattr(self.prob, "local_state", None)
+        if tiled is not None:
+            return tiled(self.part, Qglobal)
         return local_state(self.prob, self.part, Qglobal)
 
     def _check(self, code, what):
@@ -161,6 +166,32 @@ class RhsB200:
         if a.size != self.size:
             raise ValueError(f"{name} has {a.size} values, this RHS expects {self.size}")
         return a
+
+    def _host_result(self):
+        """A fresh numpy array the caller owns, backed by page-locked memory from torch's caching host allocator
+        (so the D2H copy runs at full PCIe speed and a later H2D of the same array -- e.g. as the JVP's cached
+        rhs -- does too)."""
+        torch = self._tm()
+        return torch.empty(self.size, dtype=torch.float64, pin_memory=True).numpy()
+
+    def _to_host(self, t):
+        """Device result -> numpy (through a reusable pinned buffer; synchronises)."""
+        torch = self._tm()
+        out = torch.empty(t.numel(), dtype=torch.float64, pin_memory=True)
+        out.copy_(t.view(-1), non_blocking=True)
+        torch.cuda.current_stream(t.device).synchronize()
+        return out.numpy()
+
+    def timing_history(self, max_evals=256):
+        """Device durations of the most recent evaluations, oldest first: array (k, 3) in ms
+        [traces(+pack), main (incl. the halo wait on a multi-rank handle), total] and array (k,) of modes
+        (-1 RHS, 0 FD-JVP, 1 rational JVP).  Synchronises."""
+        ms = (ctypes.c_float * (3 * max_evals))()
+        md = (ctypes.c_int * max_evals)()
+        k = self._lib.wxb_timing_history(self._h, max_evals, ctypes.byref(ms), ctypes.byref(md))
+        if k < 0:
+            self._check(k, "wxb_timing_history")
+        return numpy.array(ms[: 3 * k], dtype=numpy.float64).reshape(k, 3), numpy.array(md[:k], dtype=numpy.int64)
 
     # ---- halo exchange between ranks (NCCL through torch.distributed) -------------------------------
     def _exchange(self, stream):
@@ -213,10 +244,14 @@ class RhsB200:
         if len(self.timestamps) > 0:
             self.retrieve_last_times()
         if isinstance(q, numpy.ndarray):
-            if self.nranks != 1:
-                raise ValueError("host (numpy) states are supported on a single rank only; pass device tensors")
             a = self._as_host(q, "q")
-            out = numpy.empty_like(a)
+            if self.nranks != 1:  # halo exchange needs the split device path: H2D, evaluate, D2H
+                torch = self._tm()
+                qd = torch.from_numpy(a.reshape(-1)).to(f"cuda:{self.device_index}", non_blocking=True)
+                res = self._eval_device(qd, None, None, 0.0, 0.0, -1)
+                self.timestamps = [True]
+                return self._to_host(res).reshape(q.shape)
+            out = self._host_result()
             self._check(self._lib.wxb_rhs_host(self._h, a.ctypes.data, out.ctypes.data), "wxb_rhs_host")
             self.launches += self._kernels_per_eval()
             self._have_timing = True
@@ -237,10 +272,13 @@ class RhsB200:
         if m is None:
             raise ValueError(f"unknown JVP mode {mode!r} (complex-step is not available on this path)")
         if isinstance(Q, numpy.ndarray):
-            if self.nranks != 1:
-                raise ValueError("host (numpy) states are supported on a single rank only; pass device tensors")
             q, v, r = self._as_host(Q, "Q"), self._as_host(vec, "vec"), self._as_host(rhs0, "rhs")
-            out = numpy.empty_like(q)
+            if self.nranks != 1:
+                torch = self._tm()
+                dev = f"cuda:{self.device_index}"
+                qd, vd, rd = (torch.from_numpy(x.reshape(-1)).to(dev, non_blocking=True) for x in (q, v, r))
+                return self._to_host(self._eval_device(qd, vd, rd, float(dt), float(eps), m))
+            out = self._host_result()
             self._check(
                 self._lib.wxb_jvp_host(self._h, q.ctypes.data, v.ctypes.data, r.ctypes.data, float(dt), float(eps), m, out.ctypes.data),
                 "wxb_jvp_host",
