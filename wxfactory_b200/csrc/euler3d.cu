@@ -34,6 +34,8 @@ struct Cfg {
     // elements per block: aim for ~256 threads
     static constexpr int EB = (N == 2) ? 16 : (N == 3) ? 8 : (N == 4) ? 4 : (N == 5) ? 2 : 1;
     static constexpr int THREADS = EB * P;
+    // resident blocks per SM the main kernel is compiled for (register budget = 65536 / (THREADS * MINB))
+    static constexpr int MINB = (N <= 4) ? 2 : 1;
     // offsets into the operator block
     static constexpr int O_DIFF = 2 * N, O_CORR = 2 * N + N * N, O_HF = 4 * N + N * N;
     static constexpr int NOPS = 4 * N + 2 * N * N;
@@ -111,38 +113,69 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
 
 
 // ------------------------------------------------------------------------------------------------------
+// Per-element bookkeeping, computed once per element by one thread and kept in shared memory so that the
+// hot loops carry no index decoding.
+struct ElemInfo {
+    long long qoff, vstride;   // (var 0, this element, node 0) in the state; distance between variables
+    long long fm[3];           // (comp 0, min-side face, pt 0) of this element in fm_i / fm_j / fm_k
+    long long fm_cs[3];        // component stride of the slab's block
+    long long fm_side[3];      // min-side -> max-side face
+    int e, k, c, ny;
+};
+
+__device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P, ElemInfo& o) {
+    const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
+    o.qoff = ep.qoff;
+    o.vstride = ep.vstride;
+    o.e = e;
+    o.k = ep.k;
+    o.c = ep.c;
+    o.ny = ep.ny;
+    const long long nz = a.nz, ny = ep.ny, nx = a.nx;
+    o.fm[0] = a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i) * F;
+    o.fm_cs[0] = nz * ny * (nx + 1) * F;
+    o.fm_side[0] = F;
+    o.fm[1] = a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl) * nx + ep.i) * F;
+    o.fm_cs[1] = nz * (ny + 1) * nx * F;
+    o.fm_side[1] = nx * F;
+    o.fm[2] = a.st.fmk[ep.s] + (((long long)ep.k * ny + ep.jl) * nx + ep.i) * F;
+    o.fm_cs[2] = (nz + 1) * ny * nx * F;
+    o.fm_side[2] = ny * nx * F;
+}
+
+// ------------------------------------------------------------------------------------------------------
 // one face point: common Rusanov flux and the own-side split rho-w pieces
 //   out[0..3] = F* rows rho, rho u1, rho u2, rho theta ; out[4] = wflux_adv* ; out[5] = wflux_pres* (own side) ;
 //   out[6] = log(p_itf own side)
 template <int N>
-__device__ __forceinline__ void face_point(const EvalArgs& a, const ElemPos& ep, int e, int f, int pt, double* out7,
-                                           long long out_stride) {
+__device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei, int f, int pt, double* out7) {
     constexpr int F = N * N;
     const int d = f >> 1, side = f & 1;
-    const long long fstride = (long long)a.E * F;
+    const long long fstride = (long long)a.E * F;  // one (var, face) plane of the trace array
+    const long long vs_own = 6 * fstride;
     double own[NVAR], nb[NVAR];
     {
-        const double* t = a.trace + ((long long)f * a.E + e) * F + pt;
+        const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) own[v] = t[v * 6 * fstride];
+        for (int v = 0; v < NVAR; ++v) own[v] = t[v * vs_own];
     }
     bool bc = false;
     if (d == 2) {
-        bc = (side == 0) ? (ep.k == 0) : (ep.k == a.nz - 1);
+        bc = (side == 0) ? (ei.k == 0) : (ei.k == a.nz - 1);
         if (!bc) {
-            const int e2 = side == 0 ? e - ep.ny * a.nx : e + ep.ny * a.nx;
+            const int e2 = side == 0 ? ei.e - ei.ny * a.nx : ei.e + ei.ny * a.nx;
             const double* t = a.trace + ((long long)(f ^ 1) * a.E + e2) * F + pt;
 #pragma unroll
-            for (int v = 0; v < NVAR; ++v) nb[v] = t[v * 6 * fstride];
+            for (int v = 0; v < NVAR; ++v) nb[v] = t[v * vs_own];
         } else {
 #pragma unroll
             for (int v = 0; v < NVAR; ++v) nb[v] = own[v];  // mirrored ghost (rhs_dfr.py:265-268)
         }
     } else {
-        const int4 t = a.nbr[(long long)f * a.C + ep.c];
+        const int4 t = a.nbr[(long long)f * a.C + ei.c];
         const int kl = pt / N, al = pt % N;
         const int pt2 = (t.w & 1) ? kl * N + (N - 1 - al) : pt;
-        const double* src = a.trace + ((long long)t.x + (long long)ep.k * t.y) * F + pt2;
+        const double* src = a.trace + ((long long)t.x + (long long)ei.k * t.y) * F + pt2;
         const long long vs = (long long)t.z * F;
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) nb[v] = src[v * vs];
@@ -156,26 +189,10 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemPos& ep,
         }
     }
     // interface metric, single-valued per physical face
-    double sg, hd0, hd1, hd2;
-    {
-        long long off, cs;
-        if (d == 0) {
-            cs = (long long)a.nz * ep.ny * (a.nx + 1) * F;
-            off = a.st.fmi[ep.s] + (((long long)ep.k * ep.ny + ep.jl) * (a.nx + 1) + ep.i + side) * F + pt;
-            const double* m = a.fmi + off;
-            sg = m[0]; hd0 = m[cs]; hd1 = m[2 * cs]; hd2 = m[3 * cs];
-        } else if (d == 1) {
-            cs = (long long)a.nz * (ep.ny + 1) * a.nx * F;
-            off = a.st.fmj[ep.s] + (((long long)ep.k * (ep.ny + 1) + ep.jl + side) * a.nx + ep.i) * F + pt;
-            const double* m = a.fmj + off;
-            sg = m[0]; hd0 = m[cs]; hd1 = m[2 * cs]; hd2 = m[3 * cs];
-        } else {
-            cs = (long long)(a.nz + 1) * ep.ny * a.nx * F;
-            off = a.st.fmk[ep.s] + (((long long)(ep.k + side) * ep.ny + ep.jl) * a.nx + ep.i) * F + pt;
-            const double* m = a.fmk + off;
-            sg = m[0]; hd0 = m[cs]; hd1 = m[2 * cs]; hd2 = m[3 * cs];
-        }
-    }
+    const double* fmbase = d == 0 ? a.fmi : (d == 1 ? a.fmj : a.fmk);
+    const double* m = fmbase + ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
+    const long long cs = ei.fm_cs[d];
+    const double sg = m[0], hd0 = m[cs], hd1 = m[2 * cs], hd2 = m[3 * cs];
     const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
     // L = max-side face of the lower element, R = min-side face of the upper element
     double L[NVAR], R[NVAR];
@@ -184,8 +201,10 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemPos& ep,
         L[v] = side ? own[v] : nb[v];
         R[v] = side ? nb[v] : own[v];
     }
-    double uL = L[1 + d] / L[0];
-    double uR = R[1 + d] / R[0];
+    const double vL = d == 0 ? L[1] : (d == 1 ? L[2] : L[3]);
+    const double vR = d == 0 ? R[1] : (d == 1 ? R[2] : R[3]);
+    double uL = vL / L[0];
+    double uR = vR / R[0];
     if (bc) {  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
         if (side == 0) uL = -uR; else uR = -uL;
     }
@@ -195,158 +214,170 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemPos& ep,
     const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR / R[0]);
     const double eig = fmax(eigL, eigR);
     const double sguL = sg * uL, sguR = sg * uR, es = eig * sg;
-    out7[0 * out_stride] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
-    out7[1 * out_stride] = 0.5 * ((sguL * L[1] + sg * hd0 * pL) + (sguR * R[1] + sg * hd0 * pR) - es * (R[1] - L[1]));
-    out7[2 * out_stride] = 0.5 * ((sguL * L[2] + sg * hd1 * pL) + (sguR * R[2] + sg * hd1 * pR) - es * (R[2] - L[2]));
-    out7[3 * out_stride] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
-    out7[4 * out_stride] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
+    out7[0 * F] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
+    out7[1 * F] = 0.5 * ((sguL * L[1] + sg * hd0 * pL) + (sguR * R[1] + sg * hd0 * pR) - es * (R[1] - L[1]));
+    out7[2 * F] = 0.5 * ((sguL * L[2] + sg * hd1 * pL) + (sguR * R[2] + sg * hd1 * pR) - es * (R[2] - L[2]));
+    out7[3 * F] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
+    out7[4 * F] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
     const double pown = side ? pL : pR;
-    out7[5 * out_stride] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
-    out7[6 * out_stride] = log(pown);
+    out7[5 * F] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
+    out7[6 * F] = log(pown);
 }
 
 
-// ------------------------------------------------------------------------------------------------------
-// main kernel: one thread per solution point, EB elements per block
 template <int N>
-__global__ void __launch_bounds__(Cfg<N>::THREADS) euler_main(const EvalArgs a) {
+struct MainSmem {
+    ElemInfo ei[Cfg<N>::EB];
+    double op[Cfg<N>::NOPS];
+    double f[Cfg<N>::EB][20][Cfg<N>::P];      // d*6 + {F_rho, F_u1, F_u2, F_theta, w_adv, w_pres}; 18 = log p; 19 = sqrtG*rho
+    double ff[Cfg<N>::EB][6][7][Cfg<N>::F];   // face results, see face_point
+};
+
+// ------------------------------------------------------------------------------------------------------
+// main kernel: one thread per solution point, EB elements per block.
+//   phase 1  interface fluxes of the block's elements -> shared memory (its registers die before phase 2)
+//   phase 2  per node: forcing first (27 Christoffel loads in flight together), then the three flux fields
+//            -> shared memory, one barrier, sum-factorised derivative + lift, assemble, epilogue
+template <int N, bool JVP>
+__global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(const EvalArgs a) {
     using C = Cfg<N>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
-    __shared__ double s_op[C::NOPS];
-    __shared__ double s_f[EB][8][P];      // 0..5 per-direction fields, 6 = log p, 7 = sqrtG*rho
-    __shared__ double s_ff[EB][6][7][F];  // face results, see face_point
+    // dynamic shared memory (more than the 48 KB static limit at n >= 4), see MainSmem
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    using SM = MainSmem<N>;
+    SM& sm = *reinterpret_cast<SM*>(smem_raw);
+    double* const s_op = sm.op;
+    ElemInfo* const s_ei = sm.ei;
+    auto& s_f = sm.f;
+    auto& s_ff = sm.ff;
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
     const int e = element_of(a, blockIdx.x * EB + le);
     const bool active = e >= 0;
     for (int t = threadIdx.x; t < C::NOPS; t += C::THREADS) s_op[t] = a.ops[t];
+    if (active && node == 0) make_info(a, e, F, P, s_ei[le]);
+    __syncthreads();
 
-    const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
-    ElemPos ep;
-    double q[NVAR], sg = 1.0, h[6], p = 1.0, u[3], inv_rho;
-    double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
-    long long mo = 0;  // offset of this node in the per-node metric arrays
-    const long long EP = (long long)a.E * P;
+    // ---- phase 1: interface fluxes, 6F face points per element ----
     if (active) {
-        ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
-        mo = (long long)e * P + node;
+        for (int fp = node; fp < 6 * F; fp += P) {
+            const int f = fp / F, pt = fp % F;
+            face_point<N>(a, s_ei[le], f, pt, &s_ff[le][f][0][pt]);
+        }
+    }
+
+    // ---- phase 2: nodes ----
+    const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
+    double q[NVAR], sg = 1.0, p = 1.0, h[6], fo[3];
+    long long qo = 0, vst = 0;
+    if (active) {
+        const ElemInfo& ei = s_ei[le];
+        qo = ei.qoff + node;
+        vst = ei.vstride;
+        const long long EP = (long long)a.E * P;
+        const long long mo = (long long)e * P + node;
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) {
-            const long long o = ep.qoff + v * ep.vstride + node;
-            q[v] = a.q[o];
-            if (a.v) q[v] += a.eps * a.v[o];
+            q[v] = a.q[qo + v * vst];
+            if (JVP) q[v] += a.eps * a.v[qo + v * vst];
         }
         sg = a.sqrtg[mo];
 #pragma unroll
         for (int c = 0; c < 6; ++c) h[c] = a.h[c * EP + mo];
-        inv_rho = 1.0 / q[0];
-        u[0] = q[1] / q[0];
-        u[1] = q[2] / q[0];
-        u[2] = q[3] / q[0];
+        double ch[27];
+#pragma unroll
+        for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
+        const double idz = a.idz[mo];
+        const double rho = q[0];
+        const double u1 = q[1] / rho, u2 = q[2] / rho, w = q[3] / rho;
         p = pressure_of(q[4]);
-        s_f[le][6][node] = log(p);
-        s_f[le][7][node] = sg * q[0];
-    }
-    (void)inv_rho;
-
-    // ---- interior derivative, direction by direction (sum-factorised) ----
+        // forcing (pde_euler_cubesphere.py:203-290)
+        {
+            const double t11 = rho * u1 * u1 + h[0] * p, t12 = rho * u1 * u2 + h[1] * p, t13 = rho * u1 * w + h[2] * p;
+            const double t22 = rho * u2 * u2 + h[3] * p, t23 = rho * u2 * w + h[4] * p, t33 = rho * w * w + h[5] * p;
 #pragma unroll
-    for (int d = 0; d < 3; ++d) {
-        // h^{d,1..3} in H_PAIRS order (11,12,13,22,23,33)
-        const double hd0 = d == 0 ? h[0] : (d == 1 ? h[1] : h[2]);
-        const double hd1 = d == 0 ? h[1] : (d == 1 ? h[3] : h[4]);
-        const double hd2 = d == 0 ? h[2] : (d == 1 ? h[4] : h[5]);
-        const double wpres = sg * hd2;
-        if (active) {
-            const double sgu = sg * u[d];
-            s_f[le][0][node] = sgu * q[0];
-            s_f[le][1][node] = sgu * q[1] + sg * hd0 * p;
-            s_f[le][2][node] = sgu * q[2] + sg * hd1 * p;
-            s_f[le][3][node] = sgu * q[4];
-            s_f[le][4][node] = sgu * q[3];
-            s_f[le][5][node] = wpres;
-        }
-        __syncthreads();
-        if (active) {
-            const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
-            const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
-            const int base = node - idx * step;
-            double dv[7] = {0, 0, 0, 0, 0, 0, 0};
-#pragma unroll
-            for (int m = 0; m < N; ++m) {
-                const double dm = s_op[C::O_DIFF + idx * N + m];
-#pragma unroll
-                for (int v = 0; v < 7; ++v) dv[v] += dm * s_f[le][v][base + m * step];
-                if (d == 2) grav += s_op[C::O_HF + idx * N + m] * s_f[le][7][base + m * step];
+            for (int i = 0; i < 3; ++i) {
+                const double* c = ch + 9 * i;
+                fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
+                        c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
             }
+            if (a.has_damp) {
+                const double dw = rho / a.tau0 * a.damp[mo];
+                fo[0] += dw * (u1 - a.damp[EP + mo]);
+                fo[1] += dw * (u2 - a.damp[2 * EP + mo]);
+                fo[2] += dw * (w - a.damp[3 * EP + mo]);
+            }
+            // gravity needs the vertical filter of sqrtG*rho: keep 1/z_eta * g * 1/sqrtG in h-independent form
+            fo[2] = fo[2];
+        }
+        // pointwise fluxes of the three directions (pde_euler_cubesphere.py:72-124)
+        double* sf = &s_f[le][0][node];
 #pragma unroll
-            for (int v = 0; v < 4; ++v) acc[v] += dv[v];
-            wacc += dv[4] + p * dv[5] + p * wpres * dv[6];
+        for (int d = 0; d < 3; ++d) {
+            const double ud = d == 0 ? u1 : (d == 1 ? u2 : w);
+            const double hd0 = d == 0 ? h[0] : (d == 1 ? h[1] : h[2]);
+            const double hd1 = d == 0 ? h[1] : (d == 1 ? h[3] : h[4]);
+            const double hd2 = d == 0 ? h[2] : (d == 1 ? h[4] : h[5]);
+            const double sgu = sg * ud;
+            sf[(d * 6 + 0) * P] = sgu * q[0];
+            sf[(d * 6 + 1) * P] = sgu * q[1] + sg * hd0 * p;
+            sf[(d * 6 + 2) * P] = sgu * q[2] + sg * hd1 * p;
+            sf[(d * 6 + 3) * P] = sgu * q[4];
+            sf[(d * 6 + 4) * P] = sgu * q[3];
+            sf[(d * 6 + 5) * P] = sg * hd2;
         }
-        __syncthreads();
-    }
-
-    // ---- interface fluxes: 6F face points per element ----
-    if (active) {
-        for (int fp = node; fp < 6 * F; fp += P) {
-            const int f = fp / F, pt = fp % F;
-            face_point<N>(a, ep, e, f, pt, &s_ff[le][f][0][pt], F);
-        }
+        sf[18 * P] = log(p);
+        sf[19 * P] = sg * rho;
+        // fold the gravity prefactor into fo[2] later: keep it in a register
+        h[0] = idz;  // h[0], h[1], h[3] are no longer needed; reuse the slot for 1/z_eta
     }
     __syncthreads();
     if (!active) return;
 
-    // ---- lift (correction) ----
+    // ---- interior derivative (sum-factorised) + lift (correction) ----
+    double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
         const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
+        const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
         const int pt = d == 0 ? kk * N + jj : (d == 1 ? kk * N + ii : jj * N + ii);
+        const double* sfd = &s_f[le][d * 6][node - idx * step];
+        const double* slp = &s_f[le][18][node - idx * step];
+        double dv[7] = {0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int m = 0; m < N; ++m) {
+            const double dm = s_op[C::O_DIFF + idx * N + m];
+#pragma unroll
+            for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * P + m * step];
+            dv[6] += dm * slp[m * step];
+            if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[P + m * step];
+        }
         const double cw = s_op[C::O_CORR + idx * 2], ce = s_op[C::O_CORR + idx * 2 + 1];
-        const double hd2 = d == 0 ? h[2] : (d == 1 ? h[4] : h[5]);
-        double cv[7];
+        const double* lo = &s_ff[le][2 * d][0][pt];
+        const double* hi = &s_ff[le][2 * d + 1][0][pt];
+        // the reference adds the lift to the derivative field by field, then combines (rhs_dfr.py:106-139)
 #pragma unroll
-        for (int v = 0; v < 7; ++v) cv[v] = cw * s_ff[le][2 * d][v][pt] + ce * s_ff[le][2 * d + 1][v][pt];
+        for (int v = 0; v < 7; ++v) dv[v] += cw * lo[v * F] + ce * hi[v * F];
 #pragma unroll
-        for (int v = 0; v < 4; ++v) acc[v] += cv[v];
-        wacc += cv[4] + p * cv[5] + p * (sg * hd2) * cv[6];
+        for (int v = 0; v < 4; ++v) acc[v] += dv[v];
+        const double wpres = s_f[le][d * 6 + 5][node];
+        wacc += dv[4] + p * dv[5] + p * wpres * dv[6];
     }
 
-    // ---- assemble + forcing ----
+    // ---- assemble ----
     const double inv_sg = 1.0 / sg;
     double r[NVAR];
     r[0] = -inv_sg * acc[0];
-    r[1] = -inv_sg * acc[1];
-    r[2] = -inv_sg * acc[2];
-    r[3] = -inv_sg * wacc;
+    r[1] = -inv_sg * acc[1] - fo[0];
+    r[2] = -inv_sg * acc[2] - fo[1];
+    r[3] = -inv_sg * wacc - (fo[2] + h[0] * WXB_GRAVITY * inv_sg * grav);
     r[4] = -inv_sg * acc[3];
-    {
-        const double rho = q[0], u1 = u[0], u2 = u[1], w = u[2];
-        const double t11 = rho * u1 * u1 + h[0] * p, t12 = rho * u1 * u2 + h[1] * p, t13 = rho * u1 * w + h[2] * p;
-        const double t22 = rho * u2 * u2 + h[3] * p, t23 = rho * u2 * w + h[4] * p, t33 = rho * w * w + h[5] * p;
-        double fo[3];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            const double* c = a.chris + (long long)(9 * i) * EP + mo;
-            fo[i] = 2.0 * rho * (c[0] * u1 + c[EP] * u2 + c[2 * EP] * w) + c[3 * EP] * t11 + 2.0 * c[4 * EP] * t12 +
-                    2.0 * c[5 * EP] * t13 + c[6 * EP] * t22 + 2.0 * c[7 * EP] * t23 + c[8 * EP] * t33;
-        }
-        fo[2] += a.idz[mo] * WXB_GRAVITY * inv_sg * grav;
-        if (a.has_damp) {
-            const double dw = rho / a.tau0 * a.damp[mo];
-            fo[0] += dw * (u1 - a.damp[EP + mo]);
-            fo[1] += dw * (u2 - a.damp[2 * EP + mo]);
-            fo[2] += dw * (w - a.damp[3 * EP + mo]);
-        }
-        r[1] -= fo[0];
-        r[2] -= fo[1];
-        r[3] -= fo[2];
-    }
     // ---- epilogue: plain RHS, or the finite-difference Jacobian-vector product (matvec.py:57-88) ----
 #pragma unroll
     for (int v = 0; v < NVAR; ++v) {
-        const long long o = ep.qoff + v * ep.vstride + node;
+        const long long o = qo + v * vst;
         double x = r[v];
-        if (a.mode >= 0) {
+        if (JVP) {
             x = a.dt * (x - a.rhs0[o]) / a.eps;
             if (a.mode == WXB_JVP_RAT) x = a.v[o] - 0.5 * x;
         }
@@ -365,11 +396,35 @@ int launch_main(const EvalArgs& a, cudaStream_t s) {
     const int ne = a.elist ? a.nelist : a.E;
     if (ne == 0) return 0;
     const int blocks = (ne + Cfg<N>::EB - 1) / Cfg<N>::EB;
-    euler_main<N><<<blocks, Cfg<N>::THREADS, 0, s>>>(a);
+    constexpr int smem = (int)sizeof(MainSmem<N>);
+    if (a.mode >= 0)
+        euler_main<N, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+    else
+        euler_main<N, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
+template <int N>
+int configure_main() {
+    constexpr int smem = (int)sizeof(MainSmem<N>);
+    cudaError_t e1 = cudaFuncSetAttribute(euler_main<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e2 = cudaFuncSetAttribute(euler_main<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    return (e1 == cudaSuccess && e2 == cudaSuccess) ? 0 : -1;
+}
+
 }  // namespace
+
+// opt the main kernel of order n into its dynamic shared memory size on the current device (once per handle)
+int wxb_euler_configure(int n) {
+    switch (n) {
+        case 2: return configure_main<2>();
+        case 3: return configure_main<3>();
+        case 4: return configure_main<4>();
+        case 5: return configure_main<5>();
+        case 6: return configure_main<6>();
+    }
+    return -1;
+}
 
 // pack the trace records other handles need: sendbuf[rec][var][k][F]
 __global__ void pack_kernel(const EvalArgs a, int nvar, int F, int nfaces) {

@@ -153,6 +153,10 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     for (int r = 0; r < WXB_TIMING_RING; ++r)
         for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev_ring[r][i]));
     h->ev = h->ev_ring[0];
+    if (euler && wxb_euler_configure(n) != 0) {
+        set_err(h, "cannot configure the main kernel's shared memory: %s", cudaGetErrorString(cudaGetLastError()));
+        return WXB_ECUDA;
+    }
     return WXB_OK;
 }
 

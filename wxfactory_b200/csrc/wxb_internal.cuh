@@ -84,6 +84,7 @@ struct wxb_handle {
 };
 
 // launchers implemented per equation set
+int wxb_euler_configure(int n);
 int wxb_euler_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_main(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
