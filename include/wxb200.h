@@ -101,7 +101,8 @@ typedef struct {
     const double* topo_itf; /* SW optional: hsurf on faces: i-faces then j-faces, two-sided values
                                [ (own side, neighbour side) ... ] see csrc/sw2d.cu */
     /* horizontal connectivity, pull model: for face f in (W,E,S,N) of local column c the neighbour trace of
-     * variable v, level k, face point pt lives at  trace[((base + v*vstride + k*kstride) * F) + pt']:
+     * trace field v (Euler: the 5 variables + log(rho theta); SW: the 3 variables), level k, face point pt lives at
+ *   trace[((base + v*vstride + k*kstride) * F) + pt']:
      *   nbr[(f*C + c)*4 + {0,1,2,3}] = base, kstride, vstride, flags
      *   flags bit0: reverse the along-edge node index; bits 8..: 1 + row of `xform` (0 = identity) */
     const int32_t* nbr;     /* [4*C*4] */
@@ -117,8 +118,8 @@ const char* wxb_last_error(const wxb_handle* h); /* h may be NULL: last create e
 
 /* sizes, in doubles */
 int64_t wxb_state_size(const wxb_handle* h);      /* num_var * E * P                                  */
-int64_t wxb_send_size(const wxb_handle* h);       /* nsend  * num_var * nz * F                         */
-int64_t wxb_recv_size(const wxb_handle* h);       /* nghost * num_var * nz * F                         */
+int64_t wxb_send_size(const wxb_handle* h);       /* nsend  * ntr * nz * F  (ntr trace fields: Euler 6, SW 3) */
+int64_t wxb_recv_size(const wxb_handle* h);       /* nghost * ntr * nz * F                             */
 double* wxb_send_buffer(wxb_handle* h);           /* device pointer, contiguous, record-major          */
 double* wxb_recv_buffer(wxb_handle* h);           /* device pointer (the ghost tail of the trace array) */
 

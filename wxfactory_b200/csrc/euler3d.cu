@@ -26,6 +26,7 @@
 namespace {
 
 constexpr int NVAR = 5;
+constexpr int NTR = 6;  // trace fields: the 5 variables + log(rho*theta) as extrapolated (before the exp)
 
 template <int N>
 struct Cfg {
@@ -102,9 +103,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
         }
         lo[0] = exp(lo[5]); hi[0] = exp(hi[5]);
         lo[4] = exp(lo[6]); hi[4] = exp(hi[6]);
+        // field 5 = the extrapolated log(rho*theta) itself: the face pressure and its log follow from it with one
+        // exp and no log (face_point), instead of the reference's log(exp(.)) round trip
+        lo[5] = lo[6];
+        hi[5] = hi[6];
         double* t = a.trace + (long long)e * F + pt;
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) {
+        for (int v = 0; v < NTR; ++v) {
             t[(v * 6 + 2 * d) * fstride] = lo[v];
             t[(v * 6 + 2 * d + 1) * fstride] = hi[v];
         }
@@ -153,11 +158,11 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
     const int d = f >> 1, side = f & 1;
     const long long fstride = (long long)a.E * F;  // one (var, face) plane of the trace array
     const long long vs_own = 6 * fstride;
-    double own[NVAR], nb[NVAR];
+    double own[NTR], nb[NTR];
     {
         const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) own[v] = t[v * vs_own];
+        for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
     }
     bool bc = false;
     if (d == 2) {
@@ -166,10 +171,10 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
             const int e2 = side == 0 ? ei.e - ei.ny * a.nx : ei.e + ei.ny * a.nx;
             const double* t = a.trace + ((long long)(f ^ 1) * a.E + e2) * F + pt;
 #pragma unroll
-            for (int v = 0; v < NVAR; ++v) nb[v] = t[v * vs_own];
+            for (int v = 0; v < NTR; ++v) nb[v] = t[v * vs_own];
         } else {
 #pragma unroll
-            for (int v = 0; v < NVAR; ++v) nb[v] = own[v];  // mirrored ghost (rhs_dfr.py:265-268)
+            for (int v = 0; v < NTR; ++v) nb[v] = own[v];  // mirrored ghost (rhs_dfr.py:265-268)
         }
     } else {
         const int4 t = a.nbr[(long long)f * a.C + ei.c];
@@ -178,7 +183,7 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
         const double* src = a.trace + ((long long)t.x + (long long)ei.k * t.y) * F + pt2;
         const long long vs = (long long)t.z * F;
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) nb[v] = src[v * vs];
+        for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
         const int xid = t.w >> 8;
         if (xid) {  // sender-side basis change of (rho u1, rho u2) (process_topology.py:138-175)
             const double* m = a.xform + ((long long)(xid - 1) * N + al) * 4;
@@ -195,9 +200,9 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
     const double sg = m[0], hd0 = m[cs], hd1 = m[2 * cs], hd2 = m[3 * cs];
     const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
     // L = max-side face of the lower element, R = min-side face of the upper element
-    double L[NVAR], R[NVAR];
+    double L[NTR], R[NTR];
 #pragma unroll
-    for (int v = 0; v < NVAR; ++v) {
+    for (int v = 0; v < NTR; ++v) {
         L[v] = side ? own[v] : nb[v];
         R[v] = side ? nb[v] : own[v];
     }
@@ -208,8 +213,12 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
     if (bc) {  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
         if (side == 0) uL = -uR; else uR = -uL;
     }
-    const double pL = pressure_of(L[4]);
-    const double pR = pressure_of(R[4]);
+    // face pressure p0*exp(gamma*log(Rd/p0 * rho_theta)) (pde_euler_cubesphere.py:158-160) with
+    // log(rho_theta) taken from the trace (field 5) instead of log(exp(.)): same value to rounding
+    const double lpL = WXB_LOG_P0 + WXB_GAMMA * (L[5] + WXB_LOG_RD_P0);
+    const double lpR = WXB_LOG_P0 + WXB_GAMMA * (R[5] + WXB_LOG_RD_P0);
+    const double pL = WXB_P0 * exp(WXB_GAMMA * (L[5] + WXB_LOG_RD_P0));
+    const double pR = WXB_P0 * exp(WXB_GAMMA * (R[5] + WXB_LOG_RD_P0));
     const double eigL = fabs(uL) + sqrt(hdd * WXB_GAMMA * pL / L[0]);
     const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR / R[0]);
     const double eig = fmax(eigL, eigR);
@@ -221,7 +230,7 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
     out7[4 * F] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
     const double pown = side ? pL : pR;
     out7[5 * F] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
-    out7[6 * F] = log(pown);
+    out7[6 * F] = side ? lpL : lpR;  // log(p_itf) of the own side (rhs_dfr.py:113)
 }
 
 
@@ -290,7 +299,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         const double idz = a.idz[mo];
         const double rho = q[0];
         const double u1 = q[1] / rho, u2 = q[2] / rho, w = q[3] / rho;
-        p = pressure_of(q[4]);
+        const double lg = log((WXB_RD / WXB_P0) * q[4]);
+        p = WXB_P0 * exp(WXB_GAMMA * lg);  // pde_euler_cubesphere.py:100
         // forcing (pde_euler_cubesphere.py:203-290)
         {
             const double t11 = rho * u1 * u1 + h[0] * p, t12 = rho * u1 * u2 + h[1] * p, t13 = rho * u1 * w + h[2] * p;
@@ -326,7 +336,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             sf[(d * 6 + 4) * P] = sgu * q[3];
             sf[(d * 6 + 5) * P] = sg * hd2;
         }
-        sf[18 * P] = log(p);
+        sf[18 * P] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
         sf[19 * P] = sg * rho;
         // fold the gravity prefactor into fo[2] later: keep it in a register
         h[0] = idz;  // h[0], h[1], h[3] are no longer needed; reuse the slot for 1/z_eta
@@ -448,12 +458,12 @@ __global__ void pack_kernel(const EvalArgs a, int nvar, int F, int nfaces) {
     }
 }
 
-int wxb_pack(const EvalArgs& a, int nvar, int F, cudaStream_t s) {
+int wxb_pack(const EvalArgs& a, int nvar, int F, int nfaces, cudaStream_t s) {
     if (a.nsend == 0) return 0;
     const long long total = (long long)a.nsend * nvar * a.nz * F;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    pack_kernel<<<blocks, 256, 0, s>>>(a, nvar, F, nvar == 5 ? 6 : 4);
+    pack_kernel<<<blocks, 256, 0, s>>>(a, nvar, F, nfaces);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

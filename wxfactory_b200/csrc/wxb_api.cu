@@ -52,6 +52,7 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     const int n = cfg->n;
     h->n = n;
     h->nvar = euler ? 5 : 3;
+    h->ntr = euler ? 6 : 3;  // trace fields per face point: Euler adds log(rho*theta) (see euler3d.cu)
     h->P = euler ? n * n * n : n * n;
     h->F = euler ? n * n : n;
     h->nfaces = euler ? 6 : 4;
@@ -124,12 +125,12 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     UP(h->d_xform, A->xform, (size_t)cfg->nxform * n * 4);
     UP(h->d_send, A->send, (size_t)cfg->nsend);
 
-    // trace array: local part [nvar][nfaces][E][F], then ghost records [rec][nvar][nz][F]
-    h->trace_local = (int64_t)h->nvar * h->nfaces * h->E * h->F;
-    const int64_t ghost = (int64_t)cfg->nghost * h->nvar * nz * h->F;
+    // trace array: local part [ntr][nfaces][E][F], then ghost records [rec][ntr][nz][F]
+    h->trace_local = (int64_t)h->ntr * h->nfaces * h->E * h->F;
+    const int64_t ghost = (int64_t)cfg->nghost * h->ntr * nz * h->F;
     CU(cudaMalloc((void**)&h->d_trace, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
     CU(cudaMemset(h->d_trace, 0, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
-    if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->nvar * nz * h->F * sizeof(double)));
+    if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->ntr * nz * h->F * sizeof(double)));
 
     // inner / outer element lists: an element is "outer" if one of its horizontal faces reads a ghost record
     if (cfg->nghost > 0) {
@@ -226,7 +227,7 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
     h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     CU(cudaEventRecord(h->ev[0], s));
     int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
-    if (r == 0) r = wxb_pack(a, h->nvar, h->F, s);
+    if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, s);
     if (r != 0) {
         set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;
@@ -352,10 +353,10 @@ int wxb_destroy(wxb_handle* h) {
 
 int64_t wxb_state_size(const wxb_handle* h) { return h ? (int64_t)h->nvar * h->E * h->P : 0; }
 int64_t wxb_send_size(const wxb_handle* h) {
-    return h ? (int64_t)h->cfg.nsend * h->nvar * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
+    return h ? (int64_t)h->cfg.nsend * h->ntr * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
 }
 int64_t wxb_recv_size(const wxb_handle* h) {
-    return h ? (int64_t)h->cfg.nghost * h->nvar * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
+    return h ? (int64_t)h->cfg.nghost * h->ntr * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F : 0;
 }
 double* wxb_send_buffer(wxb_handle* h) { return h ? h->d_sendbuf : nullptr; }
 double* wxb_recv_buffer(wxb_handle* h) { return h ? h->d_trace + h->trace_local : nullptr; }

@@ -12,6 +12,8 @@
 #define WXB_CVD (WXB_CPD - WXB_RD)
 #define WXB_GRAVITY 9.80616
 #define WXB_GAMMA (WXB_CPD / WXB_CVD)
+#define WXB_LOG_RD_P0 (-5.853269048356583)  // log(Rd / p0), correctly rounded
+#define WXB_LOG_P0 11.512925464970229      // log(p0)
 
 #define WXB_TIMING_RING 256
 
@@ -34,7 +36,7 @@ struct EvalArgs {
     double dt;
     int mode;             // -1 plain RHS, WXB_JVP_FD, WXB_JVP_RAT
     double* out;
-    double* trace;        // [num_var][faces][E][F] then ghost records [rec][num_var][nz][F]
+    double* trace;        // [ntr][faces][E][F] then ghost records [rec][ntr][nz][F]  (ntr: Euler 6, SW 3)
     double* sendbuf;
     const double* sqrtg;
     const double* h;
@@ -61,7 +63,7 @@ struct EvalArgs {
 struct wxb_handle {
     wxb_config cfg;
     int device;
-    int n, P, F, nvar, nfaces;
+    int n, P, F, nvar, ntr, nfaces;
     int E, C;
     SlabTab st;
     // device arrays
@@ -89,7 +91,7 @@ int wxb_euler_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_main(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_main(const EvalArgs& a, int n, cudaStream_t s);
-int wxb_pack(const EvalArgs& a, int nvar, int F, cudaStream_t s);
+int wxb_pack(const EvalArgs& a, int ntr, int F, int nfaces, cudaStream_t s);
 
 // decode a local element index into (slab, level k, local row jl, col i)
 struct ElemPos {

@@ -54,6 +54,8 @@ class RhsB200:
         self.group = process_group
         euler = problem.equations == "euler"
         self.num_var = problem.num_var
+        # trace fields per face point: the Euler kernels carry log(rho*theta) as a 6th field (csrc/euler3d.cu)
+        self.num_trace = 6 if euler else 3
         nz = problem.nz if euler else 1
         self.part = build_partition(
             problem.nh,
@@ -63,7 +65,7 @@ class RhsB200:
             problem.bnd_we,
             nranks=self.nranks,
             rank=self.rank,
-            num_var=self.num_var,
+            num_var=self.num_trace,
             nfaces=6 if euler else 4,
         )
         self._lib = capi.load()
@@ -203,7 +205,7 @@ class RhsB200:
             self._send_t = torch.as_tensor(_DevPtr(self._lib.wxb_send_buffer(self._h), ns), device=f"cuda:{self.device_index}")
             self._recv_t = torch.as_tensor(_DevPtr(self._lib.wxb_recv_buffer(self._h), nr), device=f"cuda:{self.device_index}")
             euler = self.prob.equations == "euler"
-            self._rec = self.num_var * (self.prob.nz if euler else 1) * self.prob.F
+            self._rec = self.num_trace * (self.prob.nz if euler else 1) * self.prob.F
         ops = []
         for peer, first, cnt in self.part.send_peers:
             ops.append(dist.P2POp(dist.isend, self._send_t[first * self._rec : (first + cnt) * self._rec], peer, group=self.group))
