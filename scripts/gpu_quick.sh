@@ -6,5 +6,5 @@ d=json.loads(sys.stdin.read())
 print('value %.3e  ms/step %.3f  e2e %.3e' % (d['value'], d['ms_per_step'], d['e2e']['value']))
 for k in ('roofline','roofline_jvp'):
     r=d[k]; print(k, 'frac %.3f' % r['frac'], r['launch_ms'])
-print(d['parity'])
+print(d['parity']['ok'], d['parity']['rhs_rel_err'], d['clocks'])
 "

@@ -53,13 +53,70 @@ __device__ __forceinline__ int element_of(const EvalArgs& a, int slot) {
 }
 
 // ------------------------------------------------------------------------------------------------------
-// traces
+// Element -> face extrapolation of one line of N solution points (rhs_dfr.py:50-71, operators.py:161-165).
+// rows: the element's q rows 1..3 (momenta) and the rows of log(rho), log(rho theta), each P doubles, `rs` apart.
+// Returns the 6 trace fields: rho, rho u1, rho u2, rho w, rho theta, log(rho theta); rho and rho theta are
+// extrapolated in log space.  euler_traces (what the neighbours read) and euler_main (the element's own side)
+// both call this, so the two sides of an interface see bit-identical values.
+template <int N>
+__device__ __forceinline__ void extrap_line(const double* __restrict__ ext, const double* mom, int mom_rs, const double* lrho,
+                                            const double* lrt, int base, int step, double out[NTR]) {
+    double a1 = 0.0, a2 = 0.0, a3 = 0.0, l0 = 0.0, l4 = 0.0;
+#pragma unroll
+    for (int m = 0; m < N; ++m) {
+        const double w = ext[m];
+        const int o = base + m * step;
+        a1 = fma(w, mom[o], a1);
+        a2 = fma(w, mom[mom_rs + o], a2);
+        a3 = fma(w, mom[2 * mom_rs + o], a3);
+        l0 = fma(w, lrho[o], l0);
+        l4 = fma(w, lrt[o], l4);
+    }
+    out[0] = exp(l0);
+    out[1] = a1;
+    out[2] = a2;
+    out[3] = a3;
+    out[4] = exp(l4);
+    out[5] = l4;
+}
+
+// both sides of one line at once (shares the loads); per side the same fma chain as extrap_line
+template <int N>
+__device__ __forceinline__ void extrap_line2(const double* __restrict__ ext, const double* mom, int mom_rs, const double* lrho,
+                                             const double* lrt, int base, int step, double lo[NTR], double hi[NTR]) {
+    double a[5] = {0, 0, 0, 0, 0}, b[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+    for (int m = 0; m < N; ++m) {
+        const double wl = ext[m], wh = ext[N + m];
+        const int o = base + m * step;
+        const double x[5] = {mom[o], mom[mom_rs + o], mom[2 * mom_rs + o], lrho[o], lrt[o]};
+#pragma unroll
+        for (int v = 0; v < 5; ++v) {
+            a[v] = fma(wl, x[v], a[v]);
+            b[v] = fma(wh, x[v], b[v]);
+        }
+    }
+    lo[0] = exp(a[3]); lo[1] = a[0]; lo[2] = a[1]; lo[3] = a[2]; lo[4] = exp(a[4]); lo[5] = a[4];
+    hi[0] = exp(b[3]); hi[1] = b[0]; hi[2] = b[1]; hi[3] = b[2]; hi[4] = exp(b[4]); hi[5] = b[4];
+}
+
+// line of face point pt of direction d: first node and node stride
+template <int N>
+__device__ __forceinline__ void line_of(int d, int pt, int& base, int& step) {
+    const int a1 = pt / N, a0 = pt % N;
+    if (d == 0) { base = a1 * N * N + a0 * N; step = 1; }       // pt=(k,j): line along i
+    else if (d == 1) { base = a1 * N * N + a0; step = N; }      // pt=(k,i): line along j
+    else { base = a1 * N + a0; step = N * N; }                  // pt=(j,i): line along k
+}
+
+// ------------------------------------------------------------------------------------------------------
+// traces: every element's 6 faces x 6 fields -> a.trace (read by the neighbours in euler_main, packed for other ranks)
 template <int N>
 __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a) {
     using C = Cfg<N>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
     __shared__ double s_ext[2 * N];
-    __shared__ double s_q[EB][7][P];  // 5 variables, log(rho), log(rho theta)
+    __shared__ double s_q[EB][5][P];  // rho u1, rho u2, rho w, log(rho), log(rho theta)
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
     const int e = blockIdx.x * EB + le;
@@ -67,51 +124,41 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
     if (threadIdx.x < 2 * N) s_ext[threadIdx.x] = a.ops[threadIdx.x];
     if (active) {
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
+        double x[NVAR];  // all loads first: the conditional store below must not fence them
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) {
-            const long long o = ep.qoff + v * ep.vstride + node;
-            double x = a.q[o];
-            if (a.v) x += a.eps * a.v[o];
-            s_q[le][v][node] = x;
-            if (v == 0) s_q[le][5][node] = log(x);
-            if (v == 4) s_q[le][6][node] = log(x);
+        for (int v = 0; v < NVAR; ++v) x[v] = a.q[ep.qoff + v * ep.vstride + node];
+        if (a.v) {  // the perturbed state of the FD Jacobian-vector product, kept for euler_main
+            double dv[NVAR];
+#pragma unroll
+            for (int v = 0; v < NVAR; ++v) dv[v] = a.v[ep.qoff + v * ep.vstride + node];
+#pragma unroll
+            for (int v = 0; v < NVAR; ++v) {
+                x[v] += a.eps * dv[v];
+                a.qp[ep.qoff + v * ep.vstride + node] = x[v];
+            }
         }
+        s_q[le][0][node] = x[1];
+        s_q[le][1][node] = x[2];
+        s_q[le][2][node] = x[3];
+        s_q[le][3][node] = log(x[0]);
+        s_q[le][4][node] = log(x[4]);
     }
     __syncthreads();
     if (!active) return;
-    // 3F lines per element, each yields the min-side and max-side face value
-    const long long fstride = (long long)a.E * F;  // one (var, face) plane of the trace array
+    // 3F lines per element; each yields the min-side and the max-side face value (same arithmetic per side as
+    // extrap_line, which euler_main uses for the element's own side)
+    const long long fstride = (long long)a.E * F;  // one (field, face) plane of the trace array
     for (int ln = node; ln < 3 * F; ln += P) {
         const int d = ln / F, pt = ln % F;
-        const int a1 = pt / N, a0 = pt % N;
         int base, step;
-        if (d == 0) { base = a1 * N * N + a0 * N; step = 1; }           // pt=(k,j): line along i
-        else if (d == 1) { base = a1 * N * N + a0; step = N; }          // pt=(k,i): line along j
-        else { base = a1 * N + a0; step = N * N; }                      // pt=(j,i): line along k
-        double lo[7], hi[7];
-#pragma unroll
-        for (int v = 0; v < 7; ++v) { lo[v] = 0.0; hi[v] = 0.0; }
-#pragma unroll
-        for (int m = 0; m < N; ++m) {
-            const double wl = s_ext[m], wh = s_ext[N + m];
-#pragma unroll
-            for (int v = 0; v < 7; ++v) {
-                const double x = s_q[le][v][base + m * step];
-                lo[v] += wl * x;
-                hi[v] += wh * x;
-            }
-        }
-        lo[0] = exp(lo[5]); hi[0] = exp(hi[5]);
-        lo[4] = exp(lo[6]); hi[4] = exp(hi[6]);
-        // field 5 = the extrapolated log(rho*theta) itself: the face pressure and its log follow from it with one
-        // exp and no log (face_point), instead of the reference's log(exp(.)) round trip
-        lo[5] = lo[6];
-        hi[5] = hi[6];
-        double* t = a.trace + (long long)e * F + pt;
+        line_of<N>(d, pt, base, step);
+        double lo[NTR], hi[NTR];
+        extrap_line2<N>(s_ext, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, lo, hi);
+        double* t = a.trace + ((long long)(2 * d) * a.E + e) * F + pt;
 #pragma unroll
         for (int v = 0; v < NTR; ++v) {
-            t[(v * 6 + 2 * d) * fstride] = lo[v];
-            t[(v * 6 + 2 * d + 1) * fstride] = hi[v];
+            t[v * 6 * fstride] = lo[v];
+            t[v * 6 * fstride + fstride] = hi[v];
         }
     }
 }
@@ -150,49 +197,12 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
 
 // ------------------------------------------------------------------------------------------------------
 // one face point: common Rusanov flux and the own-side split rho-w pieces
+//   own / nb : the 6 trace fields of this element's side and of the facing side (already flipped / rotated)
 //   out[0..3] = F* rows rho, rho u1, rho u2, rho theta ; out[4] = wflux_adv* ; out[5] = wflux_pres* (own side) ;
-//   out[6] = log(p_itf own side)
+//   out[6] = log(p_itf own side)                 (fluxes.py:150-222,326-403,507-582; rhs_dfr.py:106-139)
 template <int N>
-__device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei, int f, int pt, double* out7) {
-    constexpr int F = N * N;
-    const int d = f >> 1, side = f & 1;
-    const long long fstride = (long long)a.E * F;  // one (var, face) plane of the trace array
-    const long long vs_own = 6 * fstride;
-    double own[NTR], nb[NTR];
-    {
-        const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
-#pragma unroll
-        for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
-    }
-    bool bc = false;
-    if (d == 2) {
-        bc = (side == 0) ? (ei.k == 0) : (ei.k == a.nz - 1);
-        if (!bc) {
-            const int e2 = side == 0 ? ei.e - ei.ny * a.nx : ei.e + ei.ny * a.nx;
-            const double* t = a.trace + ((long long)(f ^ 1) * a.E + e2) * F + pt;
-#pragma unroll
-            for (int v = 0; v < NTR; ++v) nb[v] = t[v * vs_own];
-        } else {
-#pragma unroll
-            for (int v = 0; v < NTR; ++v) nb[v] = own[v];  // mirrored ghost (rhs_dfr.py:265-268)
-        }
-    } else {
-        const int4 t = a.nbr[(long long)f * a.C + ei.c];
-        const int kl = pt / N, al = pt % N;
-        const int pt2 = (t.w & 1) ? kl * N + (N - 1 - al) : pt;
-        const double* src = a.trace + ((long long)t.x + (long long)ei.k * t.y) * F + pt2;
-        const long long vs = (long long)t.z * F;
-#pragma unroll
-        for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
-        const int xid = t.w >> 8;
-        if (xid) {  // sender-side basis change of (rho u1, rho u2) (process_topology.py:138-175)
-            const double* m = a.xform + ((long long)(xid - 1) * N + al) * 4;
-            const double b1 = m[0] * nb[1] + m[1] * nb[2];
-            const double b2 = m[2] * nb[1] + m[3] * nb[2];
-            nb[1] = b1;
-            nb[2] = b2;
-        }
-    }
+__device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
+                                              const double own[NTR], const double nb[NTR], double out7[7]) {
     // interface metric, single-valued per physical face
     const double* fmbase = d == 0 ? a.fmi : (d == 1 ? a.fmj : a.fmk);
     const double* m = fmbase + ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
@@ -223,80 +233,272 @@ __device__ __forceinline__ void face_point(const EvalArgs& a, const ElemInfo& ei
     const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR / R[0]);
     const double eig = fmax(eigL, eigR);
     const double sguL = sg * uL, sguR = sg * uR, es = eig * sg;
-    out7[0 * F] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
-    out7[1 * F] = 0.5 * ((sguL * L[1] + sg * hd0 * pL) + (sguR * R[1] + sg * hd0 * pR) - es * (R[1] - L[1]));
-    out7[2 * F] = 0.5 * ((sguL * L[2] + sg * hd1 * pL) + (sguR * R[2] + sg * hd1 * pR) - es * (R[2] - L[2]));
-    out7[3 * F] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
-    out7[4 * F] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
+    out7[0] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
+    out7[1] = 0.5 * ((sguL * L[1] + sg * hd0 * pL) + (sguR * R[1] + sg * hd0 * pR) - es * (R[1] - L[1]));
+    out7[2] = 0.5 * ((sguL * L[2] + sg * hd1 * pL) + (sguR * R[2] + sg * hd1 * pR) - es * (R[2] - L[2]));
+    out7[3] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
+    out7[4] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
     const double pown = side ? pL : pR;
-    out7[5 * F] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
-    out7[6 * F] = side ? lpL : lpR;  // log(p_itf) of the own side (rhs_dfr.py:113)
+    out7[5] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
+    out7[6] = side ? lpL : lpR;  // log(p_itf) of the own side (rhs_dfr.py:113)
 }
 
+// where the facing side's trace row (field 0, level of this element) starts, in units of F doubles; the distance
+// between fields; flags (bit0 = reversed along the edge, bits 8.. = 1 + xform row).  Vertical faces have no table.
+struct NbrRow {
+    long long row0, vs;
+    int flags;
+    bool bc;
+};
+__device__ __forceinline__ NbrRow nbr_row(const EvalArgs& a, int e, int k, int c, int ny, int f) {
+    NbrRow r;
+    r.flags = 0;
+    r.bc = false;
+    if (f >= 4) {
+        r.bc = (f == 4) ? (k == 0) : (k == a.nz - 1);
+        const int e2 = (f == 4) ? e - ny * a.nx : e + ny * a.nx;
+        r.row0 = (long long)(f ^ 1) * a.E + e2;
+        r.vs = 6LL * a.E;
+    } else {
+        const int4 t = a.nbr[(long long)f * a.C + c];
+        r.row0 = (long long)t.x + (long long)k * t.y;
+        r.vs = t.z;
+        r.flags = t.w;
+    }
+    return r;
+}
 
+// reorder / rotate the facing side's values into this element's frame (process_topology.py:128-175)
 template <int N>
+__device__ __forceinline__ void apply_xform(const EvalArgs& a, int flags, int al, double nb[NTR]) {
+    const int xid = flags >> 8;
+    if (xid) {
+        const double* m = a.xform + ((long long)(xid - 1) * N + al) * 4;
+        const double b1 = m[0] * nb[1] + m[1] * nb[2];
+        const double b2 = m[2] * nb[1] + m[3] * nb[2];
+        nb[1] = b1;
+        nb[2] = b2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// TMA bulk copy + mbarrier (sm_90+/sm_100a): one instruction moves one 8P-byte element row global -> shared
+// memory asynchronously; completion is counted in bytes on an mbarrier.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    unsigned ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+
+// Rows of the per-element shared-memory area (each P doubles).
+//   as staged by TMA:   0-4 q | 5-31 Christoffel (27) | 32 sqrtG | 33-38 h (6) | 39 1/z_eta
+//   after the node pass: 0-4 q | 5-24 flux fields (d*6 + {F_rho, F_u1, F_u2, F_theta, w_adv, w_pres}; 23 = log p;
+//                        24 = sqrtG*rho) | 25 log rho | 26 log(rho theta) | 27-39 dead -> interface results
+// A thread only ever reads and overwrites its own node's column, so the reuse needs no extra barrier.
+constexpr int R_Q = 0, R_CH = 5, R_SG = 32, R_H = 33, R_IDZ = 39, NROWS = 40;
+constexpr int R_FL = 5, R_LRHO = 25, R_LRT = 26, R_FF = 27, NFLUX = 20;
+constexpr int NMETRIC = 35;  // rows 5..39 = one contiguous device block [35][E*P] (see wxb_api.cu)
+
+// STAGED: the element rows are 16-byte multiples (even n): node data and the neighbours' trace rows come in
+// through TMA bulk copies.  Otherwise (odd n) they are loaded directly.
+template <int N>
+constexpr bool can_stage() { return (Cfg<N>::P * 8) % 16 == 0 && (Cfg<N>::F * 8) % 16 == 0; }
+
+template <int N, bool STG>
+struct MainCfg {
+    static constexpr int P = Cfg<N>::P, F = Cfg<N>::F;
+    static constexpr bool STAGED = STG && can_stage<N>();
+    // direct mode keeps only the 20 flux rows in shared memory (own traces are read back from a.trace)
+    static constexpr int RFL = STAGED ? R_FL : 0, RLOGP = RFL + 18, RSGRHO = RFL + 19;
+    static constexpr int ROWS = STAGED ? NROWS : NFLUX;
+    // interface results (6 faces x 7 values x F) reuse the dead rows when they fit
+    static constexpr bool FF_ALIAS = STAGED && (NROWS - R_FF) * P >= 42 * F;
+    static constexpr int FF_OWN = FF_ALIAS ? 1 : 42 * F;
+    static constexpr int NBR = STAGED ? 6 * NTR : 1, NBE = STAGED ? Cfg<N>::EB : 1, NBF = STAGED ? F : 1;
+};
+
+template <int N, bool STG>
 struct MainSmem {
-    ElemInfo ei[Cfg<N>::EB];
+    alignas(16) double st[MainCfg<N, STG>::ROWS][Cfg<N>::EB][Cfg<N>::P];  // row-major across the block's elements
+    alignas(16) double nb[MainCfg<N, STG>::NBR][MainCfg<N, STG>::NBE][MainCfg<N, STG>::NBF];  // facing traces [face*6+field][element][F]
+    double ff[Cfg<N>::EB][MainCfg<N, STG>::FF_OWN];
     double op[Cfg<N>::NOPS];
-    double f[Cfg<N>::EB][20][Cfg<N>::P];      // d*6 + {F_rho, F_u1, F_u2, F_theta, w_adv, w_pres}; 18 = log p; 19 = sqrtG*rho
-    double ff[Cfg<N>::EB][6][7][Cfg<N>::F];   // face results, see face_point
+    ElemInfo ei[Cfg<N>::EB];
+    NbrRow nr[Cfg<N>::EB][6];
+    unsigned long long bar[2];
 };
 
 // ------------------------------------------------------------------------------------------------------
 // main kernel: one thread per solution point, EB elements per block.
-//   phase 1  interface fluxes of the block's elements -> shared memory (its registers die before phase 2)
-//   phase 2  per node: forcing first (27 Christoffel loads in flight together), then the three flux fields
-//            -> shared memory, one barrier, sum-factorised derivative + lift, assemble, epilogue
-template <int N, bool JVP>
+//   phase 0  (STAGED) bulk copies bring the element's 40 node rows (barrier 0) and the 36 facing trace rows
+//            (barrier 1) into shared memory
+//   phase 1  per node: forcing, the flux fields of the three directions, log rho / log(rho theta)
+//   phase 2  per face point: own trace (same arithmetic as euler_traces), facing trace, Rusanov flux
+//   phase 3  per node: sum-factorised derivative + lift, assemble, epilogue
+// In JVP mode the state rows come from the perturbed state q + eps*v written by euler_traces (a.qp).
+template <int N, bool JVP, bool STG>
 __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(const EvalArgs a) {
     using C = Cfg<N>;
+    using MC = MainCfg<N, STG>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
-    // dynamic shared memory (more than the 48 KB static limit at n >= 4), see MainSmem
+    constexpr bool STAGED = MC::STAGED;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    using SM = MainSmem<N>;
+    using SM = MainSmem<N, STG>;
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
     double* const s_op = sm.op;
-    ElemInfo* const s_ei = sm.ei;
-    auto& s_f = sm.f;
-    auto& s_ff = sm.ff;
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
+    const int ne = a.elist ? a.nelist : a.E;
     const int e = element_of(a, blockIdx.x * EB + le);
     const bool active = e >= 0;
+    const double* const qsrc = JVP ? a.qp : a.q;
+    const long long EP = (long long)a.E * P;
     for (int t = threadIdx.x; t < C::NOPS; t += C::THREADS) s_op[t] = a.ops[t];
-    if (active && node == 0) make_info(a, e, F, P, s_ei[le]);
+    if (active && node == 0) make_info(a, e, F, P, sm.ei[le]);
+    if (STAGED && active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
+        const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
+        sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
+    }
+    if (STAGED && threadIdx.x == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+    }
     __syncthreads();
+    constexpr int RS = EB * P;  // distance between rows of one element
+    // interface result (face*7 + value, point): in the element's dead rows when they fit, else in its own array
+    auto ffp = [&](int fv, int pt) -> double* {
+        const int idx = fv * F + pt;
+        return MC::FF_ALIAS ? &sm.st[(MC::FF_ALIAS ? R_FF : 0) + idx / P][le][idx % P] : &sm.ff[le][MC::FF_ALIAS ? 0 : idx];
+    };
 
-    // ---- phase 1: interface fluxes, 6F face points per element ----
-    if (active) {
-        for (int fp = node; fp < 6 * F; fp += P) {
-            const int f = fp / F, pt = fp % F;
-            face_point<N>(a, s_ei[le], f, pt, &s_ff[le][f][0][pt]);
+    // ---- phase 0: start the bulk copies ----
+    if (STAGED) {
+        const int nact = min(EB, ne - (int)blockIdx.x * EB);
+        if (threadIdx.x == 0) {
+            int nrows = 0;
+            for (int el = 0; el < nact; ++el)
+                nrows += 6 - (sm.ei[el].k == 0) - (sm.ei[el].k == a.nz - 1);
+            mbar_expect_tx(&sm.bar[0], (unsigned)(nact * NROWS * P * 8));
+            mbar_expect_tx(&sm.bar[1], (unsigned)(nrows * NTR * F * 8));
+        }
+        // One elected thread per barrier issues the copies (uniform control flow -> plain UBLKCP, no per-lane
+        // serialisation); rows of consecutive elements are contiguous in global memory, so a run of elements moves
+        // as one copy.
+        if (threadIdx.x == 0) {
+            for (int el0 = 0; el0 < nact;) {  // runs of consecutive local element numbers (metric rows)
+                int L = 1;
+                while (el0 + L < nact && sm.ei[el0 + L].e == sm.ei[el0].e + L) ++L;
+                const double* src = a.chris + (long long)sm.ei[el0].e * P;
+                for (int row = R_CH; row < NROWS; ++row) bulk_g2s(&sm.st[row][el0][0], src + (long long)(row - R_CH) * EP, L * P * 8, &sm.bar[0]);
+                el0 += L;
+            }
+            for (int el0 = 0; el0 < nact;) {  // ... and of consecutive state rows (same slab)
+                int L = 1;
+                while (el0 + L < nact && sm.ei[el0 + L].qoff == sm.ei[el0].qoff + (long long)L * P) ++L;
+                const double* src = qsrc + sm.ei[el0].qoff;
+                for (int row = 0; row < NVAR; ++row) bulk_g2s(&sm.st[row][el0][0], src + row * sm.ei[el0].vstride, L * P * 8, &sm.bar[0]);
+                el0 += L;
+            }
+        } else if (threadIdx.x == 32) {
+            for (int f = 0; f < 6; ++f) {
+                for (int el0 = 0; el0 < nact;) {
+                    const NbrRow nr = sm.nr[el0][f];
+                    if (nr.bc) { ++el0; continue; }
+                    int L = 1;
+                    while (el0 + L < nact && !sm.nr[el0 + L][f].bc && sm.nr[el0 + L][f].row0 == nr.row0 + L && sm.nr[el0 + L][f].vs == nr.vs) ++L;
+                    for (int v = 0; v < NTR; ++v)
+                        bulk_g2s(&sm.nb[f * NTR + v][el0][0], a.trace + (nr.row0 + v * nr.vs) * F, L * F * 8, &sm.bar[1]);
+                    el0 += L;
+                }
+            }
         }
     }
 
-    // ---- phase 2: nodes ----
+    // ---- interface fluxes, 6F face points per element ----
+    auto do_faces = [&]() {
+        if (!active || (a.dbg & 1)) return;
+        const ElemInfo& ei = sm.ei[le];
+        for (int fp = node; fp < 6 * F; fp += P) {
+            const int f = fp / F, pt = fp % F, d = f >> 1, side = f & 1;
+            const int kl = pt / N, al = pt % N;
+            double own[NTR], nb[NTR];
+            bool bc;
+            if (STAGED) {
+                int base, step;
+                line_of<N>(d, pt, base, step);
+                extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
+                const NbrRow& nr = sm.nr[le][f];
+                bc = nr.bc;
+                const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
+#pragma unroll
+                for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : sm.nb[f * NTR + v][le][pt2];  // mirrored ghost (rhs_dfr.py:265-268)
+                apply_xform<N>(a, nr.flags, al, nb);
+            } else {
+                const long long vs_own = 6LL * a.E * F;
+                const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
+#pragma unroll
+                for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
+                const NbrRow nr = nbr_row(a, ei.e, ei.k, ei.c, ei.ny, f);
+                bc = nr.bc;
+                const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
+                const double* src = a.trace + nr.row0 * F + pt2;
+#pragma unroll
+                for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : src[v * nr.vs * F];
+                apply_xform<N>(a, nr.flags, al, nb);
+            }
+            double res[7];
+            rusanov_point<N>(a, ei, d, side, pt, bc, own, nb, res);
+#pragma unroll
+            for (int v = 0; v < 7; ++v) *ffp(f * 7 + v, pt) = res[v];
+        }
+    };
+
+    if (!STAGED) do_faces();  // direct mode: nothing to wait for, and its registers die before the node pass
+
+    // ---- phase 1: nodes ----
     const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
-    double q[NVAR], sg = 1.0, p = 1.0, h[6], fo[3];
+    double sg = 1.0, p = 1.0, gfac = 0.0, fo[3] = {0.0, 0.0, 0.0};
     long long qo = 0, vst = 0;
+    double* const col = &sm.st[0][le][node];  // this node's column (rows RS apart)
+    if (STAGED) mbar_wait(&sm.bar[0], 0);
+    if (a.dbg & 2) return;
     if (active) {
-        const ElemInfo& ei = s_ei[le];
+        const ElemInfo& ei = sm.ei[le];
         qo = ei.qoff + node;
         vst = ei.vstride;
-        const long long EP = (long long)a.E * P;
         const long long mo = (long long)e * P + node;
+        double q[NVAR], h[6];
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) {
-            q[v] = a.q[qo + v * vst];
-            if (JVP) q[v] += a.eps * a.v[qo + v * vst];
+            q[v] = STAGED ? col[(R_Q + v) * RS] : qsrc[qo + v * vst];
         }
-        sg = a.sqrtg[mo];
+        sg = STAGED ? col[R_SG * RS] : a.sqrtg[mo];
 #pragma unroll
-        for (int c = 0; c < 6; ++c) h[c] = a.h[c * EP + mo];
-        double ch[27];
+        for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : a.h[c * EP + mo];
+        gfac = STAGED ? col[R_IDZ * RS] : a.idz[mo];
+        double ch[STAGED ? 1 : 27];  // direct mode: all 27 Christoffel loads in flight together
+        if (!STAGED) {
 #pragma unroll
-        for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
-        const double idz = a.idz[mo];
+            for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
+        }
         const double rho = q[0];
         const double u1 = q[1] / rho, u2 = q[2] / rho, w = q[3] / rho;
         const double lg = log((WXB_RD / WXB_P0) * q[4]);
@@ -307,7 +509,9 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const double t22 = rho * u2 * u2 + h[3] * p, t23 = rho * u2 * w + h[4] * p, t33 = rho * w * w + h[5] * p;
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
-                const double* c = ch + 9 * i;
+                double c[9];
+#pragma unroll
+                for (int m = 0; m < 9; ++m) c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : ch[STAGED ? 0 : 9 * i + m];
                 fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
                         c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
             }
@@ -317,11 +521,9 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 fo[1] += dw * (u2 - a.damp[2 * EP + mo]);
                 fo[2] += dw * (w - a.damp[3 * EP + mo]);
             }
-            // gravity needs the vertical filter of sqrtG*rho: keep 1/z_eta * g * 1/sqrtG in h-independent form
-            fo[2] = fo[2];
         }
-        // pointwise fluxes of the three directions (pde_euler_cubesphere.py:72-124)
-        double* sf = &s_f[le][0][node];
+        // pointwise fluxes of the three directions (pde_euler_cubesphere.py:72-124) -> own column
+        double* fl = col + MC::RFL * RS;
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
             const double ud = d == 0 ? u1 : (d == 1 ? u2 : w);
@@ -329,48 +531,53 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const double hd1 = d == 0 ? h[1] : (d == 1 ? h[3] : h[4]);
             const double hd2 = d == 0 ? h[2] : (d == 1 ? h[4] : h[5]);
             const double sgu = sg * ud;
-            sf[(d * 6 + 0) * P] = sgu * q[0];
-            sf[(d * 6 + 1) * P] = sgu * q[1] + sg * hd0 * p;
-            sf[(d * 6 + 2) * P] = sgu * q[2] + sg * hd1 * p;
-            sf[(d * 6 + 3) * P] = sgu * q[4];
-            sf[(d * 6 + 4) * P] = sgu * q[3];
-            sf[(d * 6 + 5) * P] = sg * hd2;
+            fl[(d * 6 + 0) * RS] = sgu * q[0];
+            fl[(d * 6 + 1) * RS] = sgu * q[1] + sg * hd0 * p;
+            fl[(d * 6 + 2) * RS] = sgu * q[2] + sg * hd1 * p;
+            fl[(d * 6 + 3) * RS] = sgu * q[4];
+            fl[(d * 6 + 4) * RS] = sgu * q[3];
+            fl[(d * 6 + 5) * RS] = sg * hd2;
         }
-        sf[18 * P] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
-        sf[19 * P] = sg * rho;
-        // fold the gravity prefactor into fo[2] later: keep it in a register
-        h[0] = idz;  // h[0], h[1], h[3] are no longer needed; reuse the slot for 1/z_eta
+        col[MC::RLOGP * RS] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
+        col[MC::RSGRHO * RS] = sg * rho;
+        if (STAGED) {  // for the element's own traces (phase 2)
+            col[R_LRHO * RS] = log(rho);
+            col[R_LRT * RS] = log(q[4]);
+        }
     }
     __syncthreads();
+    if (STAGED) {
+        mbar_wait(&sm.bar[1], 0);
+        do_faces();
+        __syncthreads();
+    }
     if (!active) return;
 
-    // ---- interior derivative (sum-factorised) + lift (correction) ----
+    // ---- phase 3: interior derivative (sum-factorised) + lift (correction) ----
     double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
         const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
         const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
         const int pt = d == 0 ? kk * N + jj : (d == 1 ? kk * N + ii : jj * N + ii);
-        const double* sfd = &s_f[le][d * 6][node - idx * step];
-        const double* slp = &s_f[le][18][node - idx * step];
+        const double* sfd = &sm.st[MC::RFL + d * 6][le][node - idx * step];
+        const double* slp = &sm.st[MC::RLOGP][le][node - idx * step];
         double dv[7] = {0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
         for (int m = 0; m < N; ++m) {
             const double dm = s_op[C::O_DIFF + idx * N + m];
 #pragma unroll
-            for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * P + m * step];
+            for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * RS + m * step];
             dv[6] += dm * slp[m * step];
-            if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[P + m * step];
+            if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[RS + m * step];
         }
         const double cw = s_op[C::O_CORR + idx * 2], ce = s_op[C::O_CORR + idx * 2 + 1];
-        const double* lo = &s_ff[le][2 * d][0][pt];
-        const double* hi = &s_ff[le][2 * d + 1][0][pt];
         // the reference adds the lift to the derivative field by field, then combines (rhs_dfr.py:106-139)
 #pragma unroll
-        for (int v = 0; v < 7; ++v) dv[v] += cw * lo[v * F] + ce * hi[v * F];
+        for (int v = 0; v < 7; ++v) dv[v] += cw * *ffp(2 * d * 7 + v, pt) + ce * *ffp((2 * d + 1) * 7 + v, pt);
 #pragma unroll
         for (int v = 0; v < 4; ++v) acc[v] += dv[v];
-        const double wpres = s_f[le][d * 6 + 5][node];
+        const double wpres = col[(MC::RFL + d * 6 + 5) * RS];
         wacc += dv[4] + p * dv[5] + p * wpres * dv[6];
     }
 
@@ -380,7 +587,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     r[0] = -inv_sg * acc[0];
     r[1] = -inv_sg * acc[1] - fo[0];
     r[2] = -inv_sg * acc[2] - fo[1];
-    r[3] = -inv_sg * wacc - (fo[2] + h[0] * WXB_GRAVITY * inv_sg * grav);
+    r[3] = -inv_sg * wacc - (fo[2] + gfac * WXB_GRAVITY * inv_sg * grav);
     r[4] = -inv_sg * acc[3];
     // ---- epilogue: plain RHS, or the finite-difference Jacobian-vector product (matvec.py:57-88) ----
 #pragma unroll
@@ -406,20 +613,33 @@ int launch_main(const EvalArgs& a, cudaStream_t s) {
     const int ne = a.elist ? a.nelist : a.E;
     if (ne == 0) return 0;
     const int blocks = (ne + Cfg<N>::EB - 1) / Cfg<N>::EB;
-    constexpr int smem = (int)sizeof(MainSmem<N>);
-    if (a.mode >= 0)
-        euler_main<N, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
-    else
-        euler_main<N, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+    const bool stg = can_stage<N>() && (a.dbg & 4);
+    if (stg) {
+        constexpr int smem = (int)sizeof(MainSmem<N, true>);
+        if (a.mode >= 0)
+            euler_main<N, true, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+        else
+            euler_main<N, false, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+    } else {
+        constexpr int smem = (int)sizeof(MainSmem<N, false>);
+        if (a.mode >= 0)
+            euler_main<N, true, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+        else
+            euler_main<N, false, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+    }
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 template <int N>
 int configure_main() {
-    constexpr int smem = (int)sizeof(MainSmem<N>);
-    cudaError_t e1 = cudaFuncSetAttribute(euler_main<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    cudaError_t e2 = cudaFuncSetAttribute(euler_main<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    return (e1 == cudaSuccess && e2 == cudaSuccess) ? 0 : -1;
+    cudaError_t e[4];
+    e[0] = cudaFuncSetAttribute(euler_main<N, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, true>));
+    e[1] = cudaFuncSetAttribute(euler_main<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, true>));
+    e[2] = cudaFuncSetAttribute(euler_main<N, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, false>));
+    e[3] = cudaFuncSetAttribute(euler_main<N, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, false>));
+    for (auto x : e)
+        if (x != cudaSuccess) return -1;
+    return 0;
 }
 
 }  // namespace

@@ -1,6 +1,7 @@
 // C ABI of libwxb200.so (see include/wxb200.h for the contract and the reference interfaces replaced).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -103,10 +104,27 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     if (euler) memcpy(&ops[4 * n + n * n], A->hfilt, n * n * sizeof(double));
     UP(h->d_ops, ops.data(), (size_t)nops);
 
-    UP(h->d_sqrtg, A->sqrtg, EP);
-    UP(h->d_h, A->h, (euler ? 6 : 3) * EP);
-    UP(h->d_chris, A->chris, (euler ? 27 : 8) * EP);
-    if (euler) UP(h->d_idz, A->inv_dzdeta, EP);
+    if (euler) {
+        // one contiguous block [35][E*P]: Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta, the row order in which
+        // euler_main stages an element (csrc/euler3d.cu): one base pointer + a row stride address all 35 rows
+        if (!A->sqrtg || !A->h || !A->chris || !A->inv_dzdeta) {
+            set_err(h, "missing interior metric array");
+            return WXB_EINVAL;
+        }
+        CU(cudaMalloc((void**)&h->d_metric, 35 * EP * sizeof(double)));
+        h->d_chris = h->d_metric;
+        h->d_sqrtg = h->d_metric + 27 * EP;
+        h->d_h = h->d_metric + 28 * EP;
+        h->d_idz = h->d_metric + 34 * EP;
+        CU(cudaMemcpy(h->d_chris, A->chris, 27 * EP * sizeof(double), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(h->d_sqrtg, A->sqrtg, EP * sizeof(double), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(h->d_h, A->h, 6 * EP * sizeof(double), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(h->d_idz, A->inv_dzdeta, EP * sizeof(double), cudaMemcpyHostToDevice));
+    } else {
+        UP(h->d_sqrtg, A->sqrtg, EP);
+        UP(h->d_h, A->h, 3 * EP);
+        UP(h->d_chris, A->chris, 8 * EP);
+    }
     if (euler && cfg->has_damping) UP(h->d_damp, A->damp, 4 * EP);
     if (!euler && cfg->has_topo) {
         UP(h->d_topo, A->topo, 3 * EP);
@@ -172,6 +190,7 @@ void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, con
     a.mode = mode;
     a.out = out;
     a.trace = h->d_trace;
+    a.qp = h->d_qp;
     a.sendbuf = h->d_sendbuf;
     a.sqrtg = h->d_sqrtg;
     a.h = h->d_h;
@@ -197,12 +216,20 @@ void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, con
     a.has_damp = h->cfg.has_damping;
     a.has_topo = h->cfg.has_topo;
     a.tau0 = h->cfg.damp_tau0;
+    {
+        static const int dbg = getenv("WXB_KERNEL_OPTS") ? atoi(getenv("WXB_KERNEL_OPTS")) : 0;
+        a.dbg = dbg;
+    }
     a.st = h->st;
 }
 
 int check_mode(wxb_handle* h, const double* q, const double* v, const double* rhs0, double eps, int mode, double* out) {
     if (!q || !out) {
         set_err(h, "null state/output pointer");
+        return WXB_EINVAL;
+    }
+    if (h->cfg.equations == WXB_EQ_EULER3D && h->n % 2 == 0 && ((uintptr_t)q & 15)) {
+        set_err(h, "state pointer must be 16-byte aligned (element rows are moved with TMA bulk copies)");
         return WXB_EINVAL;
     }
     if (mode != -1 && mode != WXB_JVP_FD && mode != WXB_JVP_RAT) {
@@ -221,6 +248,9 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
     if (h->cfg.equations == WXB_EQ_EULER3D && h->cfg.advection_only) {
         h->traces_done = true;
         return WXB_OK;
+    }
+    if (v && !h->d_qp) {  // first JVP on this handle: scratch for the perturbed state
+        CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     }
     EvalArgs a;
     fill_args(h, a, q, v, nullptr, 0.0, eps, -1, nullptr);
@@ -338,9 +368,10 @@ int wxb_create(const wxb_config* cfg, const wxb_static_arrays* arrays, int devic
 int wxb_destroy(wxb_handle* h) {
     if (!h) return WXB_OK;
     cudaSetDevice(h->device);
-    void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo,
+    if (h->d_metric) h->d_sqrtg = h->d_h = h->d_chris = h->d_idz = nullptr;  // views into d_metric
+    void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
-                    h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf,  h->d_q,           h->d_v,
+                    h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf, h->d_qp,  h->d_q,           h->d_v,
                     h->d_r0,   h->d_out};
     for (void* p : ptrs)
         if (p) cudaFree(p);

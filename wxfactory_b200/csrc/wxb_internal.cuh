@@ -36,6 +36,7 @@ struct EvalArgs {
     double dt;
     int mode;             // -1 plain RHS, WXB_JVP_FD, WXB_JVP_RAT
     double* out;
+    double* qp;           // scratch: q + eps*v (written by the traces kernel in JVP mode, read by the main kernel)
     double* trace;        // [ntr][faces][E][F] then ghost records [rec][ntr][nz][F]  (ntr: Euler 6, SW 3)
     double* sendbuf;
     const double* sqrtg;
@@ -56,6 +57,8 @@ struct EvalArgs {
     int nelist;
     int E, C, nz, nx, nsend;
     int has_damp, has_topo;
+    int dbg;              // WXB_KERNEL_OPTS bit mask: 4 = TMA-staged variant of euler_main (even n); 1 / 2 = skip the
+                          // interface / node phase (timing experiments only, results are wrong)
     double tau0;
     SlabTab st;
 };
@@ -67,11 +70,12 @@ struct wxb_handle {
     int E, C;
     SlabTab st;
     // device arrays
+    double* d_metric;  // Euler: owner of d_chris / d_sqrtg / d_h / d_idz (one block, see wxb_api.cu)
     double *d_ops, *d_sqrtg, *d_h, *d_chris, *d_idz, *d_damp, *d_topo, *d_fmi, *d_fmj, *d_fmk, *d_topo_itf, *d_xform;
     int4* d_nbr;
     int *d_send, *d_elist_inner, *d_elist_outer;
     int n_inner, n_outer;
-    double *d_trace, *d_sendbuf;
+    double *d_trace, *d_sendbuf, *d_qp;
     int64_t trace_local;  // doubles in the local part of the trace array
     // staging for the *_host entry points
     double *d_q, *d_v, *d_r0, *d_out;
