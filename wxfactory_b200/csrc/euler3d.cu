@@ -23,6 +23,14 @@
 //   faces: 0 W(x1-) 1 E(x1+) 2 S(x2-) 3 N(x2+) 4 D(x3-) 5 U(x3+)
 #include "wxb_internal.cuh"
 
+// tuning knobs of the n = 4 instance (elements per block, resident blocks per SM the kernel is compiled for)
+#ifndef WXB_EB4
+#define WXB_EB4 1
+#endif
+#ifndef WXB_MINB4
+#define WXB_MINB4 8
+#endif
+
 namespace {
 
 constexpr int NVAR = 5;
@@ -33,10 +41,10 @@ struct Cfg {
     static constexpr int P = N * N * N;
     static constexpr int F = N * N;
     // elements per block: aim for ~256 threads
-    static constexpr int EB = (N == 2) ? 16 : (N == 3) ? 8 : (N == 4) ? 4 : (N == 5) ? 2 : 1;
+    static constexpr int EB = (N == 2) ? 16 : (N == 3) ? 8 : (N == 4) ? WXB_EB4 : (N == 5) ? 2 : 1;
     static constexpr int THREADS = EB * P;
     // resident blocks per SM the main kernel is compiled for (register budget = 65536 / (THREADS * MINB))
-    static constexpr int MINB = (N <= 4) ? 2 : 1;
+    static constexpr int MINB = (N == 4) ? WXB_MINB4 : (N < 4) ? 2 : 1;
     // offsets into the operator block
     static constexpr int O_DIFF = 2 * N, O_CORR = 2 * N + N * N, O_HF = 4 * N + N * N;
     static constexpr int NOPS = 4 * N + 2 * N * N;
@@ -202,12 +210,9 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
 //   out[6] = log(p_itf own side)                 (fluxes.py:150-222,326-403,507-582; rhs_dfr.py:106-139)
 template <int N>
 __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
-                                              const double own[NTR], const double nb[NTR], double out7[7]) {
+                                              const double own[NTR], const double nb[NTR], const double fm[4], double out7[7]) {
     // interface metric, single-valued per physical face
-    const double* fmbase = d == 0 ? a.fmi : (d == 1 ? a.fmj : a.fmk);
-    const double* m = fmbase + ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
-    const long long cs = ei.fm_cs[d];
-    const double sg = m[0], hd0 = m[cs], hd1 = m[2 * cs], hd2 = m[3 * cs];
+    const double sg = fm[0], hd0 = fm[1], hd1 = fm[2], hd2 = fm[3];
     const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
     // L = max-side face of the lower element, R = min-side face of the upper element
     double L[NTR], R[NTR];
@@ -373,7 +378,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     const long long EP = (long long)a.E * P;
     for (int t = threadIdx.x; t < C::NOPS; t += C::THREADS) s_op[t] = a.ops[t];
     if (active && node == 0) make_info(a, e, F, P, sm.ei[le]);
-    if (STAGED && active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
+    if (active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
         sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
     }
@@ -439,33 +444,35 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         for (int fp = node; fp < 6 * F; fp += P) {
             const int f = fp / F, pt = fp % F, d = f >> 1, side = f & 1;
             const int kl = pt / N, al = pt % N;
-            double own[NTR], nb[NTR];
-            bool bc;
+            double own[NTR], nb[NTR], fm[4];
+            const NbrRow& nr = sm.nr[le][f];
+            const bool bc = nr.bc;
+            const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
+            {  // interface metric: 4 loads issued before anything depends on them
+                const double* fmbase = d == 0 ? a.fmi : (d == 1 ? a.fmj : a.fmk);
+                const double* m = fmbase + ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
+                const long long cs = ei.fm_cs[d];
+                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+            }
             if (STAGED) {
                 int base, step;
                 line_of<N>(d, pt, base, step);
                 extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
-                const NbrRow& nr = sm.nr[le][f];
-                bc = nr.bc;
-                const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : sm.nb[f * NTR + v][le][pt2];  // mirrored ghost (rhs_dfr.py:265-268)
-                apply_xform<N>(a, nr.flags, al, nb);
             } else {
                 const long long vs_own = 6LL * a.E * F;
                 const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
+                const double* src = bc ? t : a.trace + nr.row0 * F + pt2;  // mirrored ghost (rhs_dfr.py:265-268)
+                const long long vs = bc ? vs_own : nr.vs * F;
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
-                const NbrRow nr = nbr_row(a, ei.e, ei.k, ei.c, ei.ny, f);
-                bc = nr.bc;
-                const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
-                const double* src = a.trace + nr.row0 * F + pt2;
 #pragma unroll
-                for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : src[v * nr.vs * F];
-                apply_xform<N>(a, nr.flags, al, nb);
+                for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
             }
+            apply_xform<N>(a, nr.flags, al, nb);
             double res[7];
-            rusanov_point<N>(a, ei, d, side, pt, bc, own, nb, res);
+            rusanov_point<N>(a, ei, d, side, pt, bc, own, nb, fm, res);
 #pragma unroll
             for (int v = 0; v < 7; ++v) *ffp(f * 7 + v, pt) = res[v];
         }
@@ -487,9 +494,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         const long long mo = (long long)e * P + node;
         double q[NVAR], h[6];
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) {
-            q[v] = STAGED ? col[(R_Q + v) * RS] : qsrc[qo + v * vst];
-        }
+        for (int v = 0; v < NVAR; ++v) q[v] = STAGED ? col[(R_Q + v) * RS] : qsrc[qo + v * vst];
         sg = STAGED ? col[R_SG * RS] : a.sqrtg[mo];
 #pragma unroll
         for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : a.h[c * EP + mo];
@@ -553,6 +558,17 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     }
     if (!active) return;
 
+    // the epilogue's operands are requested now so that their latency hides behind the derivative
+    double r0[NVAR], vv[NVAR];
+    if (JVP) {
+#pragma unroll
+        for (int v = 0; v < NVAR; ++v) r0[v] = a.rhs0[qo + v * vst];
+        if (a.mode == WXB_JVP_RAT) {
+#pragma unroll
+            for (int v = 0; v < NVAR; ++v) vv[v] = a.v[qo + v * vst];
+        }
+    }
+
     // ---- phase 3: interior derivative (sum-factorised) + lift (correction) ----
     double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
 #pragma unroll
@@ -595,8 +611,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         const long long o = qo + v * vst;
         double x = r[v];
         if (JVP) {
-            x = a.dt * (x - a.rhs0[o]) / a.eps;
-            if (a.mode == WXB_JVP_RAT) x = a.v[o] - 0.5 * x;
+            x = a.dt * (x - r0[v]) / a.eps;
+            if (a.mode == WXB_JVP_RAT) x = vv[v] - 0.5 * x;
         }
         a.out[o] = x;
     }
