@@ -65,6 +65,13 @@ def b_jvp(n):
     return 440.0 + 96.0 / n  # + v and the cached base RHS
 
 
+# DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
+# of euler_traces + euler_main, n = 4), from the `ncu --set full` capture summarised in profiles/r01_final_ncu.txt
+# (12x24x24 elements/panel, 2 654 208 nodes).  Re-measure and update when the kernels change.
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.106183e9 + 0.135102e9 + 1.113366e9 + 0.103725e9) / 2654208,
+                        "jvp": (0.212353e9 + 0.241339e9 + 1.219546e9 + 0.102115e9) / 2654208}
+
+
 # ------------------------------------------------------------------------------------------------------------
 # CPU arm: the numpy oracle on the small twin, one single-threaded replica per core (spawned before CUDA exists)
 _W = {}
@@ -359,7 +366,7 @@ def run_b200(args):
     peak, peak_src = measured_peaks()
     line = None
     if rank == 0:
-        def roof(tt, bytes_per_node, what):
+        def roof(tt, bytes_per_node, what, key):
             if len(tt) == 0:
                 return None
             sec = float(tt[:, 2].mean()) * 1e-3
@@ -370,7 +377,8 @@ def run_b200(args):
                 "peak": peak,
                 "unit": "GB/s",
                 "frac": ach / peak,
-                "traffic": None,
+                "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
+                "traffic_source": "profiles/r01_final_ncu.txt (bytes per node at 2.65 M nodes x this launch's nodes)",
                 "kernels": ["euler_traces<4>", "euler_main<4>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bytes_per_node,
@@ -414,8 +422,8 @@ def run_b200(args):
                 "how": "RhsB200.__call__(numpy) + RhsB200.jvp(numpy...) -> wxb_rhs_host / wxb_jvp_host: pinned host arrays in, numpy out",
             },
             "gpu_launches": int(launches),
-            "roofline": roof(t_rhs, b_rhs(n), "one RHS evaluation"),
-            "roofline_jvp": roof(t_jvp, b_jvp(n), "one fused FD-JVP evaluation (cached base RHS)"),
+            "roofline": roof(t_rhs, b_rhs(n), "one RHS evaluation", "rhs"),
+            "roofline_jvp": roof(t_jvp, b_jvp(n), "one fused FD-JVP evaluation (cached base RHS)", "jvp"),
             "clocks": clocks,
             "parity": parity,
             "setup_s": t_setup,

@@ -130,3 +130,18 @@ def test_timings_vocabulary(rhs_cache):
     rhs(ex["Q0"])
     rhs.retrieve_last_times()
     assert len(rhs.timings) >= 1 and all(t[2] > 0 for t in rhs.timings)
+
+
+def test_tma_staged_variant_matches_too():
+    """The TMA-staged variant of euler_main (WXB_KERNEL_OPTS=4, csrc/euler3d.cu) is selected per process: run the
+    device-path parity cases again in a child process with it switched on."""
+    import subprocess
+    import sys
+
+    env = dict(os.environ, WXB_KERNEL_OPTS="4")
+    here = os.path.abspath(__file__)
+    r = subprocess.run(
+        [sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k", "device_path or jvp_matches"],
+        env=env, capture_output=True, text=True, timeout=600,
+    )
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -27,6 +27,9 @@
 #ifndef WXB_EB4
 #define WXB_EB4 1
 #endif
+#ifndef WXB_CH3
+#define WXB_CH3 0  // 1: Christoffel symbols loaded 9 at a time (fewer registers, less memory parallelism)
+#endif
 #ifndef WXB_MINB4
 #define WXB_MINB4 8
 #endif
@@ -177,7 +180,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
 // hot loops carry no index decoding.
 struct ElemInfo {
     long long qoff, vstride;   // (var 0, this element, node 0) in the state; distance between variables
-    long long fm[3];           // (comp 0, min-side face, pt 0) of this element in fm_i / fm_j / fm_k
+    const double* fm[3];       // (comp 0, min-side face, pt 0) of this element in fm_i / fm_j / fm_k
     long long fm_cs[3];        // component stride of the slab's block
     long long fm_side[3];      // min-side -> max-side face
     int e, k, c, ny;
@@ -192,13 +195,13 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
     o.c = ep.c;
     o.ny = ep.ny;
     const long long nz = a.nz, ny = ep.ny, nx = a.nx;
-    o.fm[0] = a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i) * F;
+    o.fm[0] = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i) * F;
     o.fm_cs[0] = nz * ny * (nx + 1) * F;
     o.fm_side[0] = F;
-    o.fm[1] = a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl) * nx + ep.i) * F;
+    o.fm[1] = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl) * nx + ep.i) * F;
     o.fm_cs[1] = nz * (ny + 1) * nx * F;
     o.fm_side[1] = nx * F;
-    o.fm[2] = a.st.fmk[ep.s] + (((long long)ep.k * ny + ep.jl) * nx + ep.i) * F;
+    o.fm[2] = a.fmk + a.st.fmk[ep.s] + (((long long)ep.k * ny + ep.jl) * nx + ep.i) * F;
     o.fm_cs[2] = (nz + 1) * ny * nx * F;
     o.fm_side[2] = ny * nx * F;
 }
@@ -449,8 +452,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const bool bc = nr.bc;
             const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
             {  // interface metric: 4 loads issued before anything depends on them
-                const double* fmbase = d == 0 ? a.fmi : (d == 1 ? a.fmj : a.fmk);
-                const double* m = fmbase + ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
+                const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
                 const long long cs = ei.fm_cs[d];
                 fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
             }
@@ -500,7 +502,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : a.h[c * EP + mo];
         gfac = STAGED ? col[R_IDZ * RS] : a.idz[mo];
         double ch[STAGED ? 1 : 27];  // direct mode: all 27 Christoffel loads in flight together
-        if (!STAGED) {
+        if (!STAGED && !WXB_CH3) {
 #pragma unroll
             for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
         }
@@ -516,7 +518,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             for (int i = 0; i < 3; ++i) {
                 double c[9];
 #pragma unroll
-                for (int m = 0; m < 9; ++m) c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : ch[STAGED ? 0 : 9 * i + m];
+                for (int m = 0; m < 9; ++m)
+                    c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : (WXB_CH3 ? a.chris[(9 * i + m) * EP + mo] : ch[STAGED ? 0 : 9 * i + m]);
                 fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
                         c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
             }
