@@ -1,0 +1,80 @@
+"""Decomposition invariance on real GPUs (run under torchrun, one rank per GPU):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/multi_rank_check.py
+
+Every rank evaluates its slabs of the golden cases (RHS and fused FD-JVP, halo over NCCL); rank 0 also evaluates the
+whole sphere alone.  The N-rank result must equal the 1-rank result BIT FOR BIT (the analogue of the reference's
+test_multisize, tests/unit/restart/test_restart.py:107-149, which allows 1e-15) and match the reference's golden
+output within the parity bound.  Prints one line per case and exits non-zero on failure."""
+
+import json
+import os
+import sys
+
+import numpy
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from wxfactory_b200 import RhsB200, load_problem  # noqa: E402
+from wxfactory_b200.layout import scatter_back  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    cond = json.load(open(os.path.join(ROOT, "tests", "golden", "conditioning.json")))["cases"]
+    ok = True
+    for name in ["dcmip31_n4", "dcmip21", "dcmip31", "case6", "galewsky"]:
+        prob, ex = load_problem(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+        if (6 * prob.nh) % world:
+            if rank == 0:
+                print(f"{name}: 6*nh = {6 * prob.nh} rows do not split over {world} ranks, skipped")
+            continue
+        dt = float(ex["dt"])
+        rhs = RhsB200(prob, nranks=world, rank=rank, device=local)
+        q = torch.from_numpy(rhs.local_state(ex["Q0"])).to(dev)
+        v = torch.from_numpy(rhs.local_state(ex["v"])).to(dev)
+        out = rhs(q)
+        jv = rhs.jvp(v, dt, q, out, mode="fd")
+        torch.cuda.synchronize()
+        # gather the local pieces on rank 0
+        pieces = [None] * world
+        dist.all_gather_object(pieces, (out.cpu().numpy(), jv.cpu().numpy()))
+        if rank == 0:
+            from wxfactory_b200.partition import build_partition
+
+            R = numpy.zeros(prob.state_shape)
+            J = numpy.zeros(prob.state_shape)
+            euler = prob.equations == "euler"
+            for r in range(world):
+                part = build_partition(prob.nh, prob.nz if euler else 1, prob.n, prob.bnd_sn, prob.bnd_we, world, r)
+                scatter_back(prob, part, pieces[r][0], R)
+                scatter_back(prob, part, pieces[r][1], J)
+            one = RhsB200(prob, device=local)
+            q1 = torch.from_numpy(ex["Q0"]).to(dev)
+            R1 = one(q1)
+            J1 = one.jvp(torch.from_numpy(ex["v"]).to(dev), dt, q1, R1, mode="fd")
+            R1, J1 = R1.cpu().numpy().reshape(R.shape), J1.cpu().numpy().reshape(J.shape)
+            one.close()
+            same = numpy.array_equal(R, R1) and numpy.array_equal(J, J1)
+            err = numpy.linalg.norm(R - ex["rhs0"]) / numpy.linalg.norm(ex["rhs0"])
+            tol = max(1e-12, cond[name]["ref_rounding"])
+            good = same and err <= tol
+            ok = ok and good
+            print(f"{name}: {world} ranks vs 1 rank bit-identical={same}; vs reference {err:.2e} (bound {tol:.1e}) -> {'ok' if good else 'FAIL'}", flush=True)
+        rhs.close()
+        dist.barrier()
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) else 1)
+
+
+if __name__ == "__main__":
+    main()
