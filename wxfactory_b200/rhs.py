@@ -198,22 +198,16 @@ class RhsB200:
     # ---- halo exchange between ranks (NCCL through torch.distributed) -------------------------------
     def _exchange(self, stream):
         torch = self._tm()
-        import torch.distributed as dist
-
         if self._send_t is None:
             ns, nr = int(self._lib.wxb_send_size(self._h)), int(self._lib.wxb_recv_size(self._h))
             self._send_t = torch.as_tensor(_DevPtr(self._lib.wxb_send_buffer(self._h), ns), device=f"cuda:{self.device_index}")
             self._recv_t = torch.as_tensor(_DevPtr(self._lib.wxb_recv_buffer(self._h), nr), device=f"cuda:{self.device_index}")
             euler = self.prob.equations == "euler"
             self._rec = self.num_trace * (self.prob.nz if euler else 1) * self.prob.F
-        ops = []
-        for peer, first, cnt in self.part.send_peers:
-            ops.append(dist.P2POp(dist.isend, self._send_t[first * self._rec : (first + cnt) * self._rec], peer, group=self.group))
-        for peer, first, cnt in self.part.recv_peers:
-            ops.append(dist.P2POp(dist.irecv, self._recv_t[first * self._rec : (first + cnt) * self._rec], peer, group=self.group))
+        from .halo import exchange
+
         with torch.cuda.stream(stream):
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+            exchange(self.part, self._send_t, self._recv_t, self._rec, self.group)
 
     # ---- evaluation -------------------------------------------------------------------------------
     def _eval_device(self, q, v, rhs0, dt, eps, mode):
