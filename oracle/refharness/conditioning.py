@@ -22,7 +22,7 @@ sys.path.insert(0, _ROOT)
 from oracle import jvp_oracle  # noqa: E402
 from wxfactory_b200.problem import load_problem  # noqa: E402
 
-NAMES = ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4"]
+NAMES = ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4", "dcmip31_n5", "dcmip31_n6", "dcmip21_n5"]
 
 
 def _to_ld(o):

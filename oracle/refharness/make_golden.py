@@ -42,6 +42,10 @@ CONFIGS = {
     "dcmip21": ("dcmip21.ini", None, None),
     # dcmip31 physics at n=4 (the rhs_benchmark order, tests/rhs_benchmark/run.sh:67-71), small grid
     "dcmip31_n4": ("dcmip31.ini", {"num_solpts": 4, "num_elements_horizontal": 4, "num_elements_vertical": 4}, None),
+    # the remaining orders the C ABI accepts (rhs_benchmark sweeps n = 2..6), on the smallest grids
+    "dcmip31_n5": ("dcmip31.ini", {"num_solpts": 5, "num_elements_horizontal": 2, "num_elements_vertical": 2}, None),
+    "dcmip31_n6": ("dcmip31.ini", {"num_solpts": 6, "num_elements_horizontal": 2, "num_elements_vertical": 2}, None),
+    "dcmip21_n5": ("dcmip21.ini", {"num_solpts": 5, "num_elements_horizontal": 2, "num_elements_vertical": 2}, None),
 }
 
 

@@ -7,7 +7,7 @@ from wxfactory_b200 import EPS_FD, RhsB200, load_problem, matvec_fun
 
 cond = json.load(open(os.path.join(ROOT, "tests/golden/conditioning.json")))["cases"]
 rel = lambda a, b: float(numpy.linalg.norm(a - b) / max(numpy.linalg.norm(b), 1e-300))
-for name in ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4"]:
+for name in ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4", "dcmip31_n5", "dcmip31_n6", "dcmip21_n5"]:
     prob, ex = load_problem(os.path.join(ROOT, "tests/golden", name + ".npz"))
     rhs = RhsB200(prob)
     out = rhs(ex["Q0"])

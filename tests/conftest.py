@@ -8,7 +8,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
-GOLDEN_NAMES = ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4"]
+GOLDEN_NAMES = ["case6", "case5", "galewsky", "dcmip31", "dcmip21", "dcmip31_n4", "dcmip31_n5", "dcmip31_n6", "dcmip21_n5"]
 
 
 def pytest_configure(config):

@@ -4,8 +4,9 @@ Tolerances (FP64, BASELINE.json north_star: 1e-12 relative per RHS evaluation):
   RHS_TOL  relative L2 error of the whole RHS and of every variable, vs the reference's own output.  Where the
            reference's own float64 result is further than that from the exactly-rounded evaluation of its formulas
            (tests/golden/conditioning.json, made by oracle/refharness/conditioning.py with an 80-bit oracle: only
-           dcmip31_n4, a hydrostatic state at rest whose RHS is a 1e-10-relative residue of cancelling terms), the
-           bound is the reference's own rounding error: no other summation order can agree more closely.
+           the dcmip31_n4/n5/n6 cases, hydrostatic states at rest whose RHS is a 1e-10-relative residue of cancelling
+           terms), the bound is twice the reference's own rounding error: no other summation order can be expected to
+           agree more closely (measured: the CUDA result differs from the reference by 0.3 .. 1.0 of that error).
   JVP_TOL  FD-JVP error relative to dt*|rhs|/eps (the FD formula amplifies RHS rounding by 1/eps ~ 2900,
            SURVEY 7.3), vs the reference's matvec_fun(..., 'fd') / matvec_rat outputs
 """
@@ -27,7 +28,8 @@ with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "co
 
 
 def rhs_tol(name):
-    return max(RHS_TOL, CONDITIONING[name]["ref_rounding"])
+    # two independent roundings of the same ill-conditioned quantity differ by up to the sum of their errors
+    return max(RHS_TOL, 2 * CONDITIONING[name]["ref_rounding"])
 
 
 def var_tol(name, v):
