@@ -23,9 +23,37 @@
 //   faces: 0 W(x1-) 1 E(x1+) 2 S(x2-) 3 N(x2+) 4 D(x3-) 5 U(x3+)
 #include "wxb_internal.cuh"
 
-// tuning knobs of the n = 4 instance (elements per block, resident blocks per SM the kernel is compiled for)
+// tuning knobs per order n: elements per block (EB) and resident blocks per SM the main kernel is compiled for (MINB);
+// the defaults are the best of the sweeps recorded in profiles/ (scripts/gpu_variants.sh)
+#ifndef WXB_EB2
+#define WXB_EB2 8
+#endif
+#ifndef WXB_EB3
+#define WXB_EB3 4
+#endif
 #ifndef WXB_EB4
 #define WXB_EB4 1
+#endif
+#ifndef WXB_EB5
+#define WXB_EB5 1
+#endif
+#ifndef WXB_EB6
+#define WXB_EB6 1
+#endif
+#ifndef WXB_MINB2
+#define WXB_MINB2 8
+#endif
+#ifndef WXB_MINB3
+#define WXB_MINB3 4
+#endif
+#ifndef WXB_MINB4
+#define WXB_MINB4 8
+#endif
+#ifndef WXB_MINB5
+#define WXB_MINB5 4
+#endif
+#ifndef WXB_MINB6
+#define WXB_MINB6 3
 #endif
 #ifndef WXB_CH3
 #define WXB_CH3 0  // 1: Christoffel symbols loaded 9 at a time (fewer registers, less memory parallelism)
@@ -44,10 +72,10 @@ struct Cfg {
     static constexpr int P = N * N * N;
     static constexpr int F = N * N;
     // elements per block: aim for ~256 threads
-    static constexpr int EB = (N == 2) ? 16 : (N == 3) ? 8 : (N == 4) ? WXB_EB4 : (N == 5) ? 2 : 1;
+    static constexpr int EB = (N == 2) ? WXB_EB2 : (N == 3) ? WXB_EB3 : (N == 4) ? WXB_EB4 : (N == 5) ? WXB_EB5 : WXB_EB6;
     static constexpr int THREADS = EB * P;
     // resident blocks per SM the main kernel is compiled for (register budget = 65536 / (THREADS * MINB))
-    static constexpr int MINB = (N == 4) ? WXB_MINB4 : (N < 4) ? 2 : 1;
+    static constexpr int MINB = (N == 2) ? WXB_MINB2 : (N == 3) ? WXB_MINB3 : (N == 4) ? WXB_MINB4 : (N == 5) ? WXB_MINB5 : WXB_MINB6;
     // offsets into the operator block
     static constexpr int O_DIFF = 2 * N, O_CORR = 2 * N + N * N, O_HF = 4 * N + N * N;
     static constexpr int NOPS = 4 * N + 2 * N * N;
