@@ -263,3 +263,181 @@ def check_against_small(tiled: TiledEulerProblem, part, local_out, small_out):
         return 0.0, 0
     per_var = torch.sqrt(num / torch.clamp(den, min=1e-300))
     return float(per_var.max()), count
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Shallow water (BASELINE.json configs[0]/[1]: case6 / galewsky "at high element count")
+class TiledSwProblem:
+    """Tiled shallow-water problem: element (j, i) of the big panel uses base element (j mod bh, i mod bh) of a
+    problem built by the reference (tests/golden/case6.npz or galewsky.npz, no topography).  Duck-types what
+    ``RhsB200`` reads from a ``SwProblem``."""
+
+    equations = "shallow_water"
+    num_var = 3
+    hsurf = None
+
+    def __init__(self, base, nh: int):
+        if base.equations == "euler" or base.hsurf is not None:
+            raise ValueError("the shallow-water tiling takes a shallow-water base problem without topography")
+        self.base = base
+        self.n, self.nh, self.bh = base.n, int(nh), base.nh
+        self.P, self.F = base.P, base.F
+        self.case_number = base.case_number
+        for k in ("ext_w", "ext_e", "diff", "corr"):
+            setattr(self, k, getattr(base, k))
+        n = self.n
+        em = numpy.arange(self.nh) % self.bh
+        node = (em[:, None] * n + numpy.arange(n)[None, :]).ravel()
+        self.bnd_sn = numpy.ascontiguousarray(base.bnd_sn[:, node])
+        self.bnd_we = numpy.ascontiguousarray(base.bnd_we[:, node])
+
+    @property
+    def elems_per_panel(self):
+        return self.nh * self.nh
+
+    @property
+    def panel_shape(self):
+        return (3, self.nh, self.nh, self.P)
+
+    @property
+    def state_shape(self):
+        return (6,) + self.panel_shape
+
+    @property
+    def num_nodes(self):
+        return 6 * self.elems_per_panel * self.P
+
+    @property
+    def num_dofs(self):
+        return 3 * self.num_nodes
+
+    def _ji(self, sl):
+        return numpy.arange(sl.j0, sl.j1) % self.bh, numpy.arange(self.nh) % self.bh
+
+    def _node_field(self, part, arr, lead):
+        a = arr.reshape((6,) + lead + (self.bh, self.bh, self.P))
+        out = []
+        for sl in part.slabs:
+            jj, ii = self._ji(sl)
+            out.append(a[sl.panel][..., jj[:, None], ii[None, :], :].reshape(lead + (-1,)))
+        return numpy.ascontiguousarray(numpy.concatenate(out, axis=-1))
+
+    def local_static(self, part):
+        b = self.base
+        out = {
+            "ext_w": b.ext_w,
+            "ext_e": b.ext_e,
+            "diff": b.diff,
+            "corr": b.corr,
+            "sqrtg": self._node_field(part, b.sqrtg, ()),
+            "h": self._node_field(part, b.h, (3,)),
+            "chris": self._node_field(part, b.chris, (8,)),
+        }
+        hf = _face_index(self.nh, self.bh)
+        fi, fj = [], []
+        for sl in part.slabs:
+            jj, ii = self._ji(sl)
+            jf = hf[sl.j0 : sl.j1 + 1]
+            fi.append(b.fm_i[sl.panel][:, jj[:, None], hf[None, :], :].ravel())
+            fj.append(b.fm_j[sl.panel][:, jf[:, None], ii[None, :], :].ravel())
+        out["fm_i"], out["fm_j"] = numpy.concatenate(fi), numpy.concatenate(fj)
+        out["nbr"] = numpy.ascontiguousarray(part.nbr, dtype=numpy.int32)
+        out["xform"] = numpy.ascontiguousarray(part.xform, dtype=numpy.float64)
+        out["send"] = numpy.ascontiguousarray(part.send, dtype=numpy.int32)
+        return {k: (v if v.dtype == numpy.int32 else numpy.ascontiguousarray(v, dtype=numpy.float64)) for k, v in out.items()}
+
+    def local_state(self, part, base_Q):
+        q = numpy.asarray(base_Q).reshape((6, 3, self.bh, self.bh, self.P))
+        pieces = []
+        for sl in part.slabs:
+            jj, ii = self._ji(sl)
+            pieces.append(q[sl.panel][:, jj[:, None], ii[None, :], :].ravel())
+        return numpy.concatenate(pieces)
+
+    def _all(self):
+        from .partition import slabs_of_rank
+
+        class _All:
+            slabs = slabs_of_rank(self.nh, 1, 0)
+
+        return _All
+
+    def materialize(self):
+        """The whole tiled problem as a dense SwProblem (oracle-sized grids only)."""
+        from .problem import SwProblem
+
+        b, allp = self.base, self._all()
+        E, P = self.elems_per_panel, self.P
+
+        def per_panel(arr, lead):
+            a = self._node_field(allp, arr, lead).reshape(lead + (6, E, P))
+            return numpy.ascontiguousarray(numpy.moveaxis(a, len(lead), 0))
+
+        hh = numpy.arange(self.nh) % self.bh
+        hf = _face_index(self.nh, self.bh)
+        ix = numpy.ix_
+        return SwProblem(
+            n=self.n,
+            nh=self.nh,
+            case_number=b.case_number,
+            ext_w=b.ext_w,
+            ext_e=b.ext_e,
+            diff=b.diff,
+            corr=b.corr,
+            sqrtg=per_panel(b.sqrtg, ()),
+            h=per_panel(b.h, (3,)),
+            chris=per_panel(b.chris, (8,)),
+            fm_i=numpy.stack([b.fm_i[p][ix(range(3), hh, hf)] for p in range(6)]),
+            fm_j=numpy.stack([b.fm_j[p][ix(range(3), hf, hh)] for p in range(6)]),
+            bnd_sn=self.bnd_sn,
+            bnd_we=self.bnd_we,
+        )
+
+    def global_state(self, base_Q):
+        return self.local_state(self._all(), base_Q).reshape(self.state_shape)
+
+
+def sw_base_state(base_Q0, seed=20261106, amplitude=1e-3):
+    """Admissible perturbed shallow-water state on the base block (h > 0 kept by the multiplicative noise)."""
+    rng = numpy.random.default_rng(seed)
+    Q = numpy.array(base_Q0, dtype=numpy.float64, copy=True)
+    Q *= 1.0 + amplitude * rng.standard_normal(Q.shape)
+    h = Q[:, 0]
+    Q[:, 1] += h * 1e-7 * rng.standard_normal(h.shape)
+    Q[:, 2] += h * 1e-7 * rng.standard_normal(h.shape)
+    return Q
+
+
+def check_sw_against_small(tiled: TiledSwProblem, part, local_out, small_out):
+    """Shallow-water counterpart of ``check_against_small``: elements not on a panel edge are compared with the
+    2bh x 2bh twin's element of the same residue class.  Returns (worst per-variable relative L2 error, count)."""
+    import torch
+
+    out = local_out if isinstance(local_out, torch.Tensor) else torch.from_numpy(numpy.ascontiguousarray(local_out))
+    dev = out.device
+    small = torch.from_numpy(numpy.ascontiguousarray(small_out)).to(dev)
+    nh, P = tiled.nh, tiled.P
+    ipos, ism = residue_map(nh, tiled.bh)
+    num = torch.zeros(3, dtype=torch.float64, device=dev)
+    den = torch.zeros(3, dtype=torch.float64, device=dev)
+    off = count = 0
+    t = lambda a: torch.from_numpy(numpy.ascontiguousarray(a)).to(dev)  # noqa: E731
+    for sl in part.slabs:
+        cnt = 3 * sl.ny * nh * P
+        blk = out[off : off + cnt].view(3, sl.ny, nh, P)
+        off += cnt
+        jglob = numpy.arange(sl.j0, sl.j1)
+        keep = (jglob >= 1) & (jglob <= nh - 2)
+        if not keep.any():
+            continue
+        jl = numpy.nonzero(keep)[0]
+        r = jglob[keep] % tiled.bh
+        jsm = numpy.where(r == 0, tiled.bh, r)
+        got = blk[:, t(jl)][:, :, t(ipos)]
+        want = small[sl.panel][:, t(jsm)][:, :, t(ism)]
+        num += ((got - want) ** 2).sum(dim=(1, 2, 3))
+        den += (want**2).sum(dim=(1, 2, 3))
+        count += len(jl) * len(ipos)
+    if count == 0:
+        return 0.0, 0
+    return float(torch.sqrt(num / torch.clamp(den, min=1e-300)).max()), count
