@@ -17,6 +17,9 @@
  *                        and end_communication ... forcing_terms     (wx_factory/rhs/rhs_dfr.py:174-313)
  *   wxb_rhs_host / wxb_jvp_host
  *                     <- the same calls with HOST buffers (what the reference's CPU integrators hold)
+ *   wxb_linearize_host / wxb_bind_host / wxb_jvp_bound_host
+ *                     <- MatvecOp.__init__ capturing (dt, Q, rhs) and MatvecOp.__call__(vec)
+ *                        (wx_factory/solvers/matvec.py:7-34,71-73; wx_factory/integrators/ros2.py:29)
  *   wxb_timings       <- RHS.retrieve_last_times / Device.elapsed (wx_factory/rhs/rhs.py:72-73,
  *                        wx_factory/device/device.py:201-214)
  *   wxb_destroy, wxb_last_error, wxb_version : lifetime / error convention (the reference raises Python
@@ -140,10 +143,25 @@ int wxb_traces(wxb_handle* h, const double* q, const double* v, double eps, void
 int wxb_finish(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps,
                int mode /* -1 = plain RHS */, int part, double* out, void* stream);
 
-/* Same as wxb_rhs / wxb_jvp with HOST buffers: H2D copy, kernels, D2H copy, synchronise. */
+/* Same as wxb_rhs / wxb_jvp with HOST buffers: H2D copy, kernels, D2H copy, synchronise.  For the 3-D Euler
+ * equations the state moves in chunks of vertical levels on three streams, so that the upload of one chunk, the
+ * kernels of the previous one and the download of the one before overlap (env WXB_HOST_CHUNKS, default 12;
+ * page-locked host buffers are needed for the copies to run asynchronously). */
 int wxb_rhs_host(wxb_handle* h, const double* q_host, double* dq_host);
 int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, const double* rhs0_host, double dt,
                  double eps, int mode, double* out_host);
+
+/* Linearisation point kept on the device: what MatvecOp / MatvecOpRat capture at construction
+ * (wx_factory/solvers/matvec.py:7-34,71-73; built once per time step by wx_factory/integrators/ros2.py:29 and the
+ * EPI integrators, then applied once per Krylov iteration).
+ *   wxb_linearize_host : rhs_host = RHS(q_host), and (q, RHS(q)) stay on the device as the linearisation point
+ *   wxb_bind_host      : upload a (q, rhs0) pair computed elsewhere as the linearisation point
+ *   wxb_jvp_bound_host : the matvec at that point; only v goes up and the product comes down
+ * The point stays valid until the next wxb_linearize_host / wxb_bind_host on the handle (wxb_rhs_host and
+ * wxb_jvp_host do not disturb it).  WXB_ESTATE without one. */
+int wxb_linearize_host(wxb_handle* h, const double* q_host, double* rhs_host);
+int wxb_bind_host(wxb_handle* h, const double* q_host, const double* rhs0_host);
+int wxb_jvp_bound_host(wxb_handle* h, const double* v_host, double dt, double eps, int mode, double* out_host);
 
 /* Device time of the last evaluation's kernels in ms: [0] traces(+pack), [1] main, [2] total. */
 int wxb_timings(wxb_handle* h, float out_ms[3]);

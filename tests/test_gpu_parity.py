@@ -147,3 +147,51 @@ def test_tma_staged_variant_matches_too():
         env=env, capture_output=True, text=True, timeout=600,
     )
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("name", ["dcmip31", "dcmip21", "dcmip31_n4", "case6"])
+def test_host_pipeline_is_bit_identical_to_device_path(rhs_cache, name):
+    """wxb_rhs_host / wxb_jvp_host move the state in chunks of levels on three streams (wxb_api.cu): same kernels,
+    same numbers as the device-resident entry points."""
+    import torch
+
+    rhs, prob, ex = rhs_cache(name)
+    dt = float(ex["dt"])
+    dev = lambda a: torch.from_numpy(numpy.ascontiguousarray(a)).cuda()  # noqa: E731
+    want_r = rhs(dev(ex["Q0"])).cpu().numpy()
+    want_j = rhs.jvp(dev(ex["v"]), dt, dev(ex["Q0"]), dev(ex["rhs0"]), mode="fd").cpu().numpy()
+    for _ in range(2):
+        assert numpy.array_equal(rhs(ex["Q0"]), want_r)
+        assert numpy.array_equal(rhs.jvp(ex["v"], dt, ex["Q0"], ex["rhs0"], mode="fd"), want_j.ravel())
+
+
+@pytest.mark.parametrize("name", ["dcmip21", "galewsky"])
+def test_linearized_operator_keeps_its_point_on_the_device(rhs_cache, name):
+    """RhsB200.linearize / MatvecOpRat / MatvecOpFd (MatvecOp of wx_factory/solvers/matvec.py:7-34,71-73)."""
+    from wxfactory_b200 import MatvecOpFd, MatvecOpRat, matvec_fun, matvec_rat
+
+    rhs, prob, ex = rhs_cache(name)
+    dt = float(ex["dt"])
+    Q, v = ex["Q0"], ex["v"].ravel()
+    r0 = rhs(Q)
+    want_fd = matvec_fun(v, dt, Q, r0, rhs, "fd")
+    want_rat = matvec_rat(v, dt, Q, r0, rhs)
+    op = rhs.linearize(Q, dt)
+    assert op.shape == Q.shape and op.size == Q.size and op.dtype == Q.dtype
+    assert numpy.array_equal(op.rhs, r0)
+    assert numpy.array_equal(op(v), want_fd)
+    # other evaluations on the handle do not disturb the linearisation point
+    Q2 = Q * (1.0 + 1e-4)
+    r2 = rhs(Q2)
+    assert numpy.array_equal(op(v), want_fd)
+    # a second operator takes the device slot; the first one re-binds itself when used again
+    A = MatvecOpRat(dt, Q2, r2, rhs.full)
+    want2 = matvec_rat(v, dt, Q2, r2, rhs)
+    assert numpy.array_equal(A(v), want2)
+    assert numpy.array_equal(op(v), want_fd)
+    assert numpy.array_equal(A(v), want2)
+    assert numpy.array_equal(MatvecOpRat(dt, Q, r0, rhs)(v), want_rat)
+    assert numpy.array_equal(MatvecOpFd(dt, Q, r0, rhs)(v), want_fd)
+    # a foreign RHS callable goes through the generic formula
+    f = lambda x: 2.0 * x  # noqa: E731
+    assert numpy.allclose(MatvecOpFd(dt, Q, f(Q), f)(v), 2.0 * dt * v, rtol=1e-6, atol=1e-6 * dt * numpy.abs(v).max())

@@ -7,4 +7,4 @@ host-side mirror of the reference's RHS / matvec interface.
 
 from .device import B200Device  # noqa: F401
 from .problem import EulerProblem, SwProblem, load_problem, save_problem  # noqa: F401
-from .rhs import EPS_FD, MatvecOpRat, RhsB200, RhsBundleB200, matvec_fun, matvec_rat  # noqa: F401
+from .rhs import EPS_FD, MatvecOpB200, MatvecOpFd, MatvecOpRat, RhsB200, RhsBundleB200, matvec_fun, matvec_rat  # noqa: F401

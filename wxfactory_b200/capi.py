@@ -79,6 +79,9 @@ EXPORTS = [
     "wxb_finish",
     "wxb_rhs_host",
     "wxb_jvp_host",
+    "wxb_linearize_host",
+    "wxb_bind_host",
+    "wxb_jvp_bound_host",
     "wxb_timings",
     "wxb_timing_history",
 ]
@@ -117,6 +120,9 @@ def load():
     lib.wxb_finish.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, i32, vp, vp]
     lib.wxb_rhs_host.argtypes = [vp, vp, vp]
     lib.wxb_jvp_host.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp]
+    lib.wxb_linearize_host.argtypes = [vp, vp, vp]
+    lib.wxb_bind_host.argtypes = [vp, vp, vp]
+    lib.wxb_jvp_bound_host.argtypes = [vp, vp, dbl, dbl, i32, vp]
     lib.wxb_timings.argtypes = [vp, ctypes.POINTER(ctypes.c_float * 3)]
     lib.wxb_timing_history.argtypes = [vp, i32, vp, vp]
     lib.wxb_timing_history.restype = i32

@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
     __shared__ double s_q[EB][5][P];  // rho u1, rho u2, rho w, log(rho), log(rho theta)
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
-    const int e = blockIdx.x * EB + le;
-    const bool active = e < a.E;
+    const int e = element_of(a, blockIdx.x * EB + le);  // all elements, or those of a.elist (chunked host path)
+    const bool active = e >= 0;
     if (threadIdx.x < 2 * N) s_ext[threadIdx.x] = a.ops[threadIdx.x];
     if (active) {
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
@@ -651,7 +651,9 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
 
 template <int N>
 int launch_traces(const EvalArgs& a, cudaStream_t s) {
-    const int blocks = (a.E + Cfg<N>::EB - 1) / Cfg<N>::EB;
+    const int ne = a.elist ? a.nelist : a.E;
+    if (ne == 0) return 0;
+    const int blocks = (ne + Cfg<N>::EB - 1) / Cfg<N>::EB;
     euler_traces<N><<<blocks, Cfg<N>::THREADS, 0, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -37,8 +37,9 @@ __global__ void __launch_bounds__(Cfg2<N>::THREADS) sw_traces(const EvalArgs a) 
     __shared__ double s_ext[2 * N];
     __shared__ double s_q[EB][NVAR][P];
     const int le = threadIdx.x / P, node = threadIdx.x % P;
-    const int e = blockIdx.x * EB + le;
-    const bool active = e < a.E;
+    const int slot = blockIdx.x * EB + le;
+    const int e = a.elist ? (slot < a.nelist ? a.elist[slot] : -1) : (slot < a.E ? slot : -1);
+    const bool active = e >= 0;
     if (threadIdx.x < 2 * N) s_ext[threadIdx.x] = a.ops[threadIdx.x];
     if (active) {
         const ElemPos ep = decode_elem(a.st, e, 1, a.nx, P, NVAR);
@@ -321,7 +322,9 @@ __global__ void __launch_bounds__(Cfg2<N>::THREADS, Cfg2<N>::MINB) sw_main(const
 
 template <int N>
 int launch_traces2(const EvalArgs& a, cudaStream_t s) {
-    const int blocks = (a.E + Cfg2<N>::EB - 1) / Cfg2<N>::EB;
+    const int ne = a.elist ? a.nelist : a.E;
+    if (ne == 0) return 0;
+    const int blocks = (ne + Cfg2<N>::EB - 1) / Cfg2<N>::EB;
     sw_traces<N><<<blocks, Cfg2<N>::THREADS, 0, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

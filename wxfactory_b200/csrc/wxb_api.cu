@@ -372,12 +372,21 @@ int wxb_destroy(wxb_handle* h) {
     void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
                     h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf, h->d_qp,  h->d_q,           h->d_v,
-                    h->d_r0,   h->d_out};
+                    h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int r = 0; r < WXB_TIMING_RING; ++r)
         for (int i = 0; i < 3; ++i)
             if (h->ev_ring[r][i]) cudaEventDestroy(h->ev_ring[r][i]);
+    if (h->pipe_ready) {
+        for (int c = 0; c < h->nchunk; ++c) {
+            cudaEventDestroy(h->ev_in[c]);
+            cudaEventDestroy(h->ev_main[c]);
+        }
+        cudaStreamDestroy(h->s_in);
+        cudaStreamDestroy(h->s_cmp);
+        cudaStreamDestroy(h->s_out);
+    }
     delete h;
     return WXB_OK;
 }
@@ -460,14 +469,154 @@ static int host_stage(wxb_handle* h) {
     return WXB_OK;
 }
 
+// ---- chunked host pipeline ----------------------------------------------------------------------------------
+// The host entry points move a whole state each way over PCIe; done back to back (upload, kernels, download) the
+// link idles in one direction at a time.  For the 3-D Euler equations the state is cut into chunks of vertical
+// levels: horizontal neighbours live on the same level, vertical ones at most one level away, so the main kernel of
+// chunk c only needs the traces of chunks <= c+1.  Upload of chunk c+2, kernels of chunk c and download of chunk
+// c-1 then run concurrently on three streams.  Shallow water (one level) degenerates to one chunk.
+static int pipe_setup(wxb_handle* h) {
+    if (h->pipe_ready) return WXB_OK;
+    int r = host_stage(h);
+    if (r != WXB_OK) return r;
+    const bool euler = h->cfg.equations == WXB_EQ_EULER3D;
+    const int nz = euler ? h->cfg.nz : 1;
+    int want = getenv("WXB_HOST_CHUNKS") ? atoi(getenv("WXB_HOST_CHUNKS")) : 12;
+    if (want < 1) want = 1;
+    if (want > WXB_MAX_CHUNKS) want = WXB_MAX_CHUNKS;
+    h->nchunk = nz < want ? nz : want;
+    std::vector<int> list((size_t)h->E);
+    int pos = 0;
+    for (int c = 0; c < h->nchunk; ++c) {
+        const int k0 = (int)((long long)c * nz / h->nchunk), k1 = (int)((long long)(c + 1) * nz / h->nchunk);
+        h->chunk_k[c] = k0;
+        h->chunk_off[c] = pos;
+        for (int s = 0; s < h->st.nslabs; ++s) {
+            const int per_level = h->st.ny[s] * h->cfg.nx;
+            for (int el = k0 * per_level; el < k1 * per_level; ++el) list[pos++] = h->st.ebase[s] + el;
+        }
+    }
+    h->chunk_k[h->nchunk] = nz;
+    h->chunk_off[h->nchunk] = pos;
+    if (pos != h->E) {
+        set_err(h, "internal: chunk lists cover %d of %d elements", pos, h->E);
+        return WXB_ESTATE;
+    }
+    UP(h->d_clist, list.data(), list.size());
+    CU(cudaStreamCreate(&h->s_in));
+    CU(cudaStreamCreate(&h->s_cmp));
+    CU(cudaStreamCreate(&h->s_out));
+    for (int c = 0; c < h->nchunk; ++c) {
+        CU(cudaEventCreateWithFlags(&h->ev_in[c], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_main[c], cudaEventDisableTiming));
+    }
+    h->pipe_ready = true;
+    return WXB_OK;
+}
+
+// copy the levels of chunk c of one state-shaped array (per slab: nvar rows of contiguous levels)
+static int chunk_copy(wxb_handle* h, int c, double* dst, const double* src, cudaMemcpyKind kind, cudaStream_t s) {
+    if (h->nchunk == 1) {
+        CU(cudaMemcpyAsync(dst, src, (size_t)wxb_state_size(h) * sizeof(double), kind, s));
+        return WXB_OK;
+    }
+    const int nz = h->cfg.nz;
+    const int k0 = h->chunk_k[c], k1 = h->chunk_k[c + 1];
+    for (int sl = 0; sl < h->st.nslabs; ++sl) {
+        const size_t level = (size_t)h->st.ny[sl] * h->cfg.nx * h->P;  // doubles per level of this slab
+        const size_t off = (size_t)h->nvar * h->P * h->st.ebase[sl] + (size_t)k0 * level;
+        const size_t pitch = (size_t)nz * level * sizeof(double);
+        CU(cudaMemcpy2DAsync(dst + off, pitch, src + off, pitch, (size_t)(k1 - k0) * level * sizeof(double), h->nvar, kind, s));
+    }
+    return WXB_OK;
+}
+
+// One evaluation with host operands.  *_host == nullptr means "already on the device" (in the matching d_* array).
+static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, double* d_v, const double* v_host, double* d_r0,
+                          const double* r0_host, double dt, double eps, int mode, double* d_out, double* out_host) {
+    CU(cudaSetDevice(h->device));
+    const bool euler = h->cfg.equations == WXB_EQ_EULER3D;
+    const bool jvp = mode >= 0;
+    int r = check_mode(h, d_q, jvp ? d_v : nullptr, jvp ? d_r0 : nullptr, eps, mode, d_out);
+    if (r != WXB_OK) return r;
+    if (jvp && !h->d_qp) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
+    const int nc = h->nchunk;
+    // uploads, chunk by chunk
+    for (int c = 0; c < nc; ++c) {
+        if (q_host && (r = chunk_copy(h, c, d_q, q_host, cudaMemcpyHostToDevice, h->s_in)) != WXB_OK) return r;
+        if (jvp && v_host && (r = chunk_copy(h, c, d_v, v_host, cudaMemcpyHostToDevice, h->s_in)) != WXB_OK) return r;
+        if (jvp && r0_host && (r = chunk_copy(h, c, d_r0, r0_host, cudaMemcpyHostToDevice, h->s_in)) != WXB_OK) return r;
+        CU(cudaEventRecord(h->ev_in[c], h->s_in));
+    }
+    EvalArgs at, am;
+    fill_args(h, at, d_q, jvp ? d_v : nullptr, nullptr, 0.0, eps, -1, nullptr);
+    fill_args(h, am, d_q, jvp ? d_v : nullptr, jvp ? d_r0 : nullptr, dt, eps, mode, d_out);
+    h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
+    cudaStream_t sc = h->s_cmp;
+    CU(cudaEventRecord(h->ev[0], sc));
+    auto traces = [&](int c) -> int {
+        if (nc > 1) {
+            at.elist = h->d_clist + h->chunk_off[c];
+            at.nelist = h->chunk_off[c + 1] - h->chunk_off[c];
+        }
+        return euler ? wxb_euler_traces(at, h->n, sc) : wxb_sw_traces(at, h->n, sc);
+    };
+    auto maink = [&](int c) -> int {
+        if (nc > 1) {
+            am.elist = h->d_clist + h->chunk_off[c];
+            am.nelist = h->chunk_off[c + 1] - h->chunk_off[c];
+        }
+        return euler ? wxb_euler_main(am, h->n, sc) : wxb_sw_main(am, h->n, sc);
+    };
+    for (int c = 0; c <= nc; ++c) {
+        if (c < nc) {
+            CU(cudaStreamWaitEvent(sc, h->ev_in[c], 0));
+            if (traces(c) != 0) {
+                set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+                return WXB_ECUDA;
+            }
+            if (c == nc - 1) CU(cudaEventRecord(h->ev[1], sc));
+        }
+        if (c >= 1) {  // traces of chunks <= c are in flight: chunk c-1 has everything it reads
+            if (maink(c - 1) != 0) {
+                set_err(h, "main kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+                return WXB_ECUDA;
+            }
+            CU(cudaEventRecord(h->ev_main[c - 1], sc));
+            CU(cudaStreamWaitEvent(h->s_out, h->ev_main[c - 1], 0));
+            if (out_host && (r = chunk_copy(h, c - 1, out_host, d_out, cudaMemcpyDeviceToHost, h->s_out)) != WXB_OK) return r;
+        }
+    }
+    CU(cudaEventRecord(h->ev[2], sc));
+    h->ev_mode[h->nevals % WXB_TIMING_RING] = mode;
+    h->nevals++;
+    h->timed = true;
+    h->traces_done = false;
+    CU(cudaStreamSynchronize(h->s_out));
+    CU(cudaStreamSynchronize(sc));
+    return WXB_OK;
+}
+
+// hosts entry points are for handles without remote neighbours; the advection-only short cut keeps the plain path
+static int host_ready(wxb_handle* h, bool* plain) {
+    if (h->cfg.nghost != 0) {
+        set_err(h, "handle has remote neighbours: use wxb_traces / exchange / wxb_finish");
+        return WXB_ESTATE;
+    }
+    *plain = h->cfg.equations == WXB_EQ_EULER3D && h->cfg.advection_only;
+    return *plain ? host_stage(h) : pipe_setup(h);
+}
+
 int wxb_rhs_host(wxb_handle* h, const double* q_host, double* dq_host) {
     if (!h) return WXB_EINVAL;
     if (!q_host || !dq_host) {
         set_err(h, "null host pointer");
         return WXB_EINVAL;
     }
-    int r = host_stage(h);
+    bool plain;
+    int r = host_ready(h, &plain);
     if (r != WXB_OK) return r;
+    if (!plain) return pipelined_eval(h, h->d_q, q_host, nullptr, nullptr, nullptr, nullptr, 0.0, 0.0, -1, h->d_out, dq_host);
     const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
     CU(cudaMemcpyAsync(h->d_q, q_host, bytes, cudaMemcpyHostToDevice, 0));
     r = wxb_rhs(h, h->d_q, h->d_out, nullptr);
@@ -484,13 +633,100 @@ int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, cons
         set_err(h, "null host pointer");
         return WXB_EINVAL;
     }
-    int r = host_stage(h);
+    if (mode < 0) {
+        set_err(h, "wxb_jvp_host needs mode WXB_JVP_FD or WXB_JVP_RAT");
+        return WXB_EINVAL;
+    }
+    bool plain;
+    int r = host_ready(h, &plain);
     if (r != WXB_OK) return r;
+    if (!plain) return pipelined_eval(h, h->d_q, q_host, h->d_v, v_host, h->d_r0, rhs0_host, dt, eps, mode, h->d_out, out_host);
     const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
     CU(cudaMemcpyAsync(h->d_q, q_host, bytes, cudaMemcpyHostToDevice, 0));
     CU(cudaMemcpyAsync(h->d_v, v_host, bytes, cudaMemcpyHostToDevice, 0));
     CU(cudaMemcpyAsync(h->d_r0, rhs0_host, bytes, cudaMemcpyHostToDevice, 0));
     r = wxb_jvp(h, h->d_q, h->d_v, h->d_r0, dt, eps, mode, h->d_out, nullptr);
+    if (r != WXB_OK) return r;
+    CU(cudaMemcpyAsync(out_host, h->d_out, bytes, cudaMemcpyDeviceToHost, 0));
+    CU(cudaStreamSynchronize(0));
+    return WXB_OK;
+}
+
+static int lin_stage(wxb_handle* h) {
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    if (!h->d_lq) {
+        CU(cudaSetDevice(h->device));
+        CU(cudaMalloc((void**)&h->d_lq, bytes));
+        CU(cudaMalloc((void**)&h->d_lr, bytes));
+    }
+    return WXB_OK;
+}
+
+int wxb_linearize_host(wxb_handle* h, const double* q_host, double* rhs_host) {
+    if (!h) return WXB_EINVAL;
+    if (!q_host || !rhs_host) {
+        set_err(h, "null host pointer");
+        return WXB_EINVAL;
+    }
+    bool plain;
+    int r = host_ready(h, &plain);
+    if (r == WXB_OK) r = lin_stage(h);
+    if (r != WXB_OK) return r;
+    h->bound = false;
+    if (!plain) {
+        r = pipelined_eval(h, h->d_lq, q_host, nullptr, nullptr, nullptr, nullptr, 0.0, 0.0, -1, h->d_lr, rhs_host);
+    } else {
+        const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+        CU(cudaMemcpyAsync(h->d_lq, q_host, bytes, cudaMemcpyHostToDevice, 0));
+        r = wxb_rhs(h, h->d_lq, h->d_lr, nullptr);
+        if (r != WXB_OK) return r;
+        CU(cudaMemcpyAsync(rhs_host, h->d_lr, bytes, cudaMemcpyDeviceToHost, 0));
+        CU(cudaStreamSynchronize(0));
+    }
+    h->bound = r == WXB_OK;
+    return r;
+}
+
+int wxb_bind_host(wxb_handle* h, const double* q_host, const double* rhs0_host) {
+    if (!h) return WXB_EINVAL;
+    if (!q_host || !rhs0_host) {
+        set_err(h, "null host pointer");
+        return WXB_EINVAL;
+    }
+    bool plain;
+    int r = host_ready(h, &plain);
+    if (r == WXB_OK) r = lin_stage(h);
+    if (r != WXB_OK) return r;
+    h->bound = false;
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    CU(cudaMemcpyAsync(h->d_lq, q_host, bytes, cudaMemcpyHostToDevice, 0));
+    CU(cudaMemcpyAsync(h->d_lr, rhs0_host, bytes, cudaMemcpyHostToDevice, 0));
+    CU(cudaStreamSynchronize(0));
+    h->bound = true;
+    return WXB_OK;
+}
+
+int wxb_jvp_bound_host(wxb_handle* h, const double* v_host, double dt, double eps, int mode, double* out_host) {
+    if (!h) return WXB_EINVAL;
+    if (!v_host || !out_host) {
+        set_err(h, "null host pointer");
+        return WXB_EINVAL;
+    }
+    if (mode < 0) {
+        set_err(h, "wxb_jvp_bound_host needs mode WXB_JVP_FD or WXB_JVP_RAT");
+        return WXB_EINVAL;
+    }
+    if (!h->bound) {
+        set_err(h, "no linearisation point: call wxb_linearize_host or wxb_bind_host first");
+        return WXB_ESTATE;
+    }
+    bool plain;
+    int r = host_ready(h, &plain);
+    if (r != WXB_OK) return r;
+    if (!plain) return pipelined_eval(h, h->d_lq, nullptr, h->d_v, v_host, h->d_lr, nullptr, dt, eps, mode, h->d_out, out_host);
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    CU(cudaMemcpyAsync(h->d_v, v_host, bytes, cudaMemcpyHostToDevice, 0));
+    r = wxb_jvp(h, h->d_lq, h->d_v, h->d_lr, dt, eps, mode, h->d_out, nullptr);
     if (r != WXB_OK) return r;
     CU(cudaMemcpyAsync(out_host, h->d_out, bytes, cudaMemcpyDeviceToHost, 0));
     CU(cudaStreamSynchronize(0));

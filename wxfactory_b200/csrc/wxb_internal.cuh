@@ -63,6 +63,8 @@ struct EvalArgs {
     SlabTab st;
 };
 
+#define WXB_MAX_CHUNKS 16
+
 struct wxb_handle {
     wxb_config cfg;
     int device;
@@ -79,6 +81,17 @@ struct wxb_handle {
     int64_t trace_local;  // doubles in the local part of the trace array
     // staging for the *_host entry points
     double *d_q, *d_v, *d_r0, *d_out;
+    // linearisation point kept on the device between wxb_linearize_host / wxb_bind_host and wxb_jvp_bound_host
+    double *d_lq, *d_lr;
+    bool bound;
+    // chunked host pipeline (k-level chunks: upload of chunk c+1, kernels of chunk c, download of chunk c-1 overlap)
+    bool pipe_ready;
+    int nchunk;
+    int chunk_k[WXB_MAX_CHUNKS + 1];    // first level of every chunk
+    int chunk_off[WXB_MAX_CHUNKS + 1];  // offsets into d_clist
+    int* d_clist;                       // elements of chunk 0, chunk 1, ...
+    cudaStream_t s_in, s_cmp, s_out;
+    cudaEvent_t ev_in[WXB_MAX_CHUNKS], ev_main[WXB_MAX_CHUNKS];
     // one event triple per evaluation, in a ring: [0] start, [1] traces(+pack) done, [2] main done
     cudaEvent_t ev_ring[WXB_TIMING_RING][3];
     int ev_mode[WXB_TIMING_RING];

@@ -286,6 +286,40 @@ class RhsB200:
         r, _ = self._as_device(rhs0, "rhs")
         return self._eval_device(q, v, r, float(dt), float(eps), m)
 
+    # ---- linearisation point kept on the device (MatvecOp, wx_factory/solvers/matvec.py:7-34,71-73) --
+    def linearize(self, Q, dt, mode="fd", eps=EPS_FD):
+        """``rhs = self(Q)`` plus the operator ``vec -> matvec_fun(vec, dt, Q, rhs, self)`` (``mode="rat"``:
+        ``matvec_rat``) in one call: returns a ``MatvecOpB200`` whose ``.rhs`` is RHS(Q) in Q's shape.  With a numpy
+        ``Q`` on a single-rank handle, Q and RHS(Q) stay on the device, so every later application moves only
+        ``vec`` up and the product down (the integrators build one operator per time step and apply it once per
+        Krylov iteration: wx_factory/integrators/ros2.py:29)."""
+        if mode not in ("fd", "rat"):
+            raise ValueError(f"unknown JVP mode {mode!r} (complex-step is not available on this path)")
+        if isinstance(Q, numpy.ndarray) and self.nranks == 1:
+            a = self._as_host(Q, "Q")
+            out = self._host_result()
+            self._check(self._lib.wxb_linearize_host(self._h, a.ctypes.data, out.ctypes.data), "wxb_linearize_host")
+            self.launches += self._kernels_per_eval()
+            self._have_timing = True
+            self.timestamps = [True]
+            self._lin_token = getattr(self, "_lin_token", 0) + 1
+            return MatvecOpB200(self, dt, Q, out.reshape(Q.shape), mode, eps, token=self._lin_token)
+        return MatvecOpB200(self, dt, Q, self(Q), mode, eps, token=None)
+
+    def _bind(self, Q, rhs0):
+        q, r = self._as_host(Q, "Q"), self._as_host(rhs0, "rhs")
+        self._check(self._lib.wxb_bind_host(self._h, q.ctypes.data, r.ctypes.data), "wxb_bind_host")
+        self._lin_token = getattr(self, "_lin_token", 0) + 1
+        return self._lin_token
+
+    def _jvp_bound(self, vec, dt, mode, eps):
+        v = self._as_host(vec, "vec")
+        out = self._host_result()
+        m = capi.JVP_FD if mode == "fd" else capi.JVP_RAT
+        self._check(self._lib.wxb_jvp_bound_host(self._h, v.ctypes.data, float(dt), float(eps), m, out.ctypes.data), "wxb_jvp_bound_host")
+        self.launches += self._kernels_per_eval()
+        return out
+
     # ---- timing vocabulary of the reference (rhs.py:68-73,190-213) ---------------------------------
     def clear_timings(self):
         self.timestamps = []
@@ -330,16 +364,68 @@ def matvec_rat(vec, dt, Q, rhs, rhs_handle):
     return vec - 0.5 * jac.flatten()
 
 
-class MatvecOpRat:
-    """wx_factory/solvers/matvec.py:71-73."""
+class MatvecOpB200:
+    """``MatvecOp`` (wx_factory/solvers/matvec.py:7-27: ``dtype``, ``shape``, ``size``, ``__call__(vec)``) for a
+    ``RhsB200``.  With host arrays on a single-rank handle the linearisation point (Q, rhs) is uploaded once -- at
+    ``RhsB200.linearize`` or at the first application -- and kept on the device; the operator is then a snapshot of
+    (Q, rhs) at that moment (the reference's closure would see later in-place changes of Q; its integrators build
+    a new operator every step instead).  Device arrays and multi-rank handles go through ``RhsB200.jvp``."""
 
-    def __init__(self, dt, Q, rhs_vec, rhs_handle):
-        self.dt, self.Q, self.rhs_vec, self.rhs_handle = dt, Q, rhs_vec, rhs_handle
+    def __init__(self, owner, dt, Q, rhs_vec, mode="fd", eps=EPS_FD, token=None):
+        self.owner, self.dt, self.Q, self.rhs, self.mode, self.eps = owner, dt, Q, rhs_vec, mode, eps
         self.dtype, self.shape = Q.dtype, tuple(Q.shape)
-        self.size = int(numpy.prod(self.shape))
+        self.size = int(math.prod(self.shape))
+        self._token = token
+        self._host = isinstance(Q, numpy.ndarray) and isinstance(rhs_vec, numpy.ndarray) and owner.nranks == 1
+
+    def matvec(self, vec):
+        return self(vec)
 
     def __call__(self, vec):
-        return matvec_rat(vec, self.dt, self.Q, self.rhs_vec, self.rhs_handle)
+        o = self.owner
+        if not (self._host and isinstance(vec, numpy.ndarray)):
+            return o.jvp(vec, self.dt, self.Q, self.rhs, mode=self.mode, eps=self.eps)
+        if self._token is None or self._token != getattr(o, "_lin_token", 0):
+            self._token = o._bind(self.Q, self.rhs)  # another operator took the handle's slot in between
+        return o._jvp_bound(vec, self.dt, self.mode, self.eps)
+
+
+class MatvecOpRat(MatvecOpB200):
+    """wx_factory/solvers/matvec.py:71-73 (same constructor); falls back to the generic formula for a foreign RHS."""
+
+    def __init__(self, dt, Q, rhs_vec, rhs_handle):
+        owner = getattr(rhs_handle, "__self__", rhs_handle)
+        self.rhs_handle = rhs_handle
+        if isinstance(owner, RhsB200):
+            super().__init__(owner, dt, Q, rhs_vec, mode="rat")
+        else:
+            self.owner, self.dt, self.Q, self.rhs = None, dt, Q, rhs_vec
+            self.dtype, self.shape = Q.dtype, tuple(Q.shape)
+            self.size = int(math.prod(self.shape))
+
+    @property
+    def rhs_vec(self):
+        return self.rhs
+
+    def __call__(self, vec):
+        if self.owner is None:
+            return matvec_rat(vec, self.dt, self.Q, self.rhs, self.rhs_handle)
+        return super().__call__(vec)
+
+
+class MatvecOpFd(MatvecOpRat):
+    """The finite-difference operator ``vec -> matvec_fun(vec, dt, Q, rhs, rhs_handle, "fd")`` the EPI / KIOPS
+    integrators wrap in a lambda (wx_factory/integrators/epi.py), as an object with the same constructor as
+    ``MatvecOpRat``."""
+
+    def __init__(self, dt, Q, rhs_vec, rhs_handle):
+        super().__init__(dt, Q, rhs_vec, rhs_handle)
+        self.mode = "fd"
+
+    def __call__(self, vec):
+        if self.owner is None:
+            return matvec_fun(vec, self.dt, self.Q, self.rhs, self.rhs_handle, "fd")
+        return MatvecOpB200.__call__(self, vec)
 
 
 class RhsBundleB200:
