@@ -62,6 +62,10 @@
 #define WXB_MINB4 8
 #endif
 
+#ifndef WXB_RCP
+#define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
+#endif
+
 namespace {
 
 constexpr int NVAR = 5;
@@ -254,8 +258,14 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     }
     const double vL = d == 0 ? L[1] : (d == 1 ? L[2] : L[3]);
     const double vR = d == 0 ? R[1] : (d == 1 ? R[2] : R[3]);
+#if WXB_RCP
+    const double rL = 1.0 / L[0], rR = 1.0 / R[0];  // one reciprocal per side serves the velocity and the sound speed
+    double uL = vL * rL;
+    double uR = vR * rR;
+#else
     double uL = vL / L[0];
     double uR = vR / R[0];
+#endif
     if (bc) {  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
         if (side == 0) uL = -uR; else uR = -uL;
     }
@@ -265,8 +275,13 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     const double lpR = WXB_LOG_P0 + WXB_GAMMA * (R[5] + WXB_LOG_RD_P0);
     const double pL = WXB_P0 * exp(WXB_GAMMA * (L[5] + WXB_LOG_RD_P0));
     const double pR = WXB_P0 * exp(WXB_GAMMA * (R[5] + WXB_LOG_RD_P0));
+#if WXB_RCP
+    const double eigL = fabs(uL) + sqrt(hdd * WXB_GAMMA * pL * rL);
+    const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR * rR);
+#else
     const double eigL = fabs(uL) + sqrt(hdd * WXB_GAMMA * pL / L[0]);
     const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR / R[0]);
+#endif
     const double eig = fmax(eigL, eigR);
     const double sguL = sg * uL, sguR = sg * uR, es = eig * sg;
     out7[0] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
@@ -302,6 +317,37 @@ __device__ __forceinline__ NbrRow nbr_row(const EvalArgs& a, int e, int k, int c
         r.flags = t.w;
     }
     return r;
+}
+
+// Everything the interface pass needs to address one face of one element, worked out once by one thread so that
+// the 6F face points only add their point index.
+struct FaceRow {
+    const double* own;  // trace field 0 of this face, point 0
+    const double* nb;   // facing side's field 0, point 0 (the own row again at a rigid boundary: mirrored ghost)
+    const double* fm;   // interface metric, component 0, point 0
+    long long nb_vs;    // distance between the facing row's fields
+    long long fm_cs;    // distance between interface-metric components
+    int flags, bc;
+};
+__device__ __forceinline__ void make_face_row(const EvalArgs& a, int e, const ElemPos& ep, int f, int F, FaceRow& o) {
+    const NbrRow r = nbr_row(a, e, ep.k, ep.c, ep.ny, f);
+    const int d = f >> 1, side = f & 1;
+    const long long nz = a.nz, ny = ep.ny, nx = a.nx;
+    o.own = a.trace + ((long long)f * a.E + e) * F;
+    o.nb = r.bc ? o.own : a.trace + r.row0 * F;
+    o.nb_vs = r.bc ? 6LL * a.E * F : r.vs * F;
+    o.flags = r.flags;
+    o.bc = r.bc;
+    if (d == 0) {
+        o.fm = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i + side) * F;
+        o.fm_cs = nz * ny * (nx + 1) * F;
+    } else if (d == 1) {
+        o.fm = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl + side) * nx + ep.i) * F;
+        o.fm_cs = nz * (ny + 1) * nx * F;
+    } else {
+        o.fm = a.fmk + a.st.fmk[ep.s] + ((((long long)ep.k + side) * ny + ep.jl) * nx + ep.i) * F;
+        o.fm_cs = (nz + 1) * ny * nx * F;
+    }
 }
 
 // reorder / rotate the facing side's values into this element's frame (process_topology.py:128-175)
@@ -379,6 +425,7 @@ struct MainSmem {
     double op[Cfg<N>::NOPS];
     ElemInfo ei[Cfg<N>::EB];
     NbrRow nr[Cfg<N>::EB][6];
+    FaceRow fr[Cfg<N>::EB][6];
     unsigned long long bar[2];
 };
 
@@ -411,7 +458,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     if (active && node == 0) make_info(a, e, F, P, sm.ei[le]);
     if (active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
-        sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
+        if (STAGED) sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
+        else make_face_row(a, e, ep, node - (P - 6), F, sm.fr[le][node - (P - 6)]);
     }
     if (STAGED && threadIdx.x == 0) {
         mbar_init(&sm.bar[0], 1);
@@ -472,35 +520,43 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     auto do_faces = [&]() {
         if (!active || (a.dbg & 1)) return;
         const ElemInfo& ei = sm.ei[le];
+        const long long vs_own = 6LL * a.E * F;
         for (int fp = node; fp < 6 * F; fp += P) {
             const int f = fp / F, pt = fp % F, d = f >> 1, side = f & 1;
             const int kl = pt / N, al = pt % N;
             double own[NTR], nb[NTR], fm[4];
-            const NbrRow& nr = sm.nr[le][f];
-            const bool bc = nr.bc;
-            const int pt2 = (nr.flags & 1) ? kl * N + (N - 1 - al) : pt;
-            {  // interface metric: 4 loads issued before anything depends on them
+            int flags;
+            bool bc;
+            if (STAGED) {
+                const NbrRow& nr = sm.nr[le][f];
+                bc = nr.bc;
+                flags = nr.flags;
+                const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
                 const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
                 const long long cs = ei.fm_cs[d];
                 fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
-            }
-            if (STAGED) {
                 int base, step;
                 line_of<N>(d, pt, base, step);
                 extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : sm.nb[f * NTR + v][le][pt2];  // mirrored ghost (rhs_dfr.py:265-268)
             } else {
-                const long long vs_own = 6LL * a.E * F;
-                const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
-                const double* src = bc ? t : a.trace + nr.row0 * F + pt2;  // mirrored ghost (rhs_dfr.py:265-268)
-                const long long vs = bc ? vs_own : nr.vs * F;
+                const FaceRow& fr = sm.fr[le][f];
+                bc = fr.bc;
+                flags = fr.flags;
+                const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
+                const double* m = fr.fm + pt;  // interface metric: 4 loads issued before anything depends on them
+                const long long cs = fr.fm_cs;
+                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+                const double* t = fr.own + pt;
+                const double* src = fr.nb + pt2;
+                const long long vs = fr.nb_vs;
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
             }
-            apply_xform<N>(a, nr.flags, al, nb);
+            apply_xform<N>(a, flags, al, nb);
             double res[7];
             rusanov_point<N>(a, ei, d, side, pt, bc, own, nb, fm, res);
 #pragma unroll
@@ -535,7 +591,12 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
         }
         const double rho = q[0];
+#if WXB_RCP
+        const double irho = 1.0 / rho;
+        const double u1 = q[1] * irho, u2 = q[2] * irho, w = q[3] * irho;
+#else
         const double u1 = q[1] / rho, u2 = q[2] / rho, w = q[3] / rho;
+#endif
         const double lg = log((WXB_RD / WXB_P0) * q[4]);
         p = WXB_P0 * exp(WXB_GAMMA * lg);  // pde_euler_cubesphere.py:100
         // forcing (pde_euler_cubesphere.py:203-290)
