@@ -66,10 +66,11 @@ def b_jvp(n):
 
 
 # DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
-# of euler_traces + euler_main, n = 4), from the `ncu --set full` capture summarised in profiles/r01_final_ncu.txt
-# (12x24x24 elements/panel, 2 654 208 nodes).  Re-measure and update when the kernels change.
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.106183e9 + 0.135102e9 + 1.113366e9 + 0.103725e9) / 2654208,
-                        "jvp": (0.212353e9 + 0.241339e9 + 1.219546e9 + 0.102115e9) / 2654208}
+# of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
+# profiles/r01_v6_full_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
+NCU_TRAFFIC_NODES = 10616832
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.424739e9 + 0.708382e9 + 4.544390e9 + 0.419160e9) / NCU_TRAFFIC_NODES,
+                        "jvp": (0.849587e9 + 1.134996e9 + 4.999879e9 + 0.424802e9) / NCU_TRAFFIC_NODES}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -381,7 +382,7 @@ def run_b200(args):
                 "unit": "GB/s",
                 "frac": ach / peak,
                 "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
-                "traffic_source": "profiles/r01_final_ncu.txt (bytes per node at 2.65 M nodes x this launch's nodes)",
+                "traffic_source": "profiles/r01_v6_full_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
                 "kernels": ["euler_traces<4>", "euler_main<4>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bytes_per_node,
@@ -444,6 +445,73 @@ def run_b200(args):
     return line
 
 
+def run_shallow_water(args):
+    """Side measurement (rank 0, one GPU): BASELINE.json configs[1] -- galewsky (n = 3) "at high element count",
+    the reference's 30x30 panels tiled to --sw-nh.  Same protocol as the headline workload: device time of every
+    evaluation from the C ABI's events, roofline against B_sw(n) = 144 + 48/n (RHS) / 192 + 48/n (JVP, + v and the
+    cached base RHS) bytes per node, parity through the tiling periodicity against the numpy oracle."""
+    import torch
+
+    from oracle import jvp_oracle
+    from wxfactory_b200 import EPS_FD, RhsB200, synthetic as syn
+    from wxfactory_b200.problem import load_problem
+
+    base, ex = load_problem(os.path.join(ROOT, "tests", "golden", "galewsky.npz"))
+    Qb = syn.sw_base_state(ex["Q0"])
+    vb = syn.base_direction(Qb)
+    dt = float(ex["dt"])
+    tiled = syn.TiledSwProblem(base, args.sw_nh)
+    rhs = RhsB200(tiled)
+    q = torch.from_numpy(rhs.local_state(Qb)).cuda()
+    v = torch.from_numpy(rhs.local_state(vb)).cuda()
+    r0 = rhs(q)
+    jv = rhs.jvp(v, dt, q, r0)
+    small = syn.TiledSwProblem(base, 2 * base.nh)
+    orc = jvp_oracle.make_oracle(small.materialize())
+    Qs, vs = small.global_state(Qb), small.global_state(vb)
+    wr = orc.rhs(Qs)
+    wj = jvp_oracle.matvec_fd(orc.rhs, vs.ravel(), dt, Qs, wr).reshape(Qs.shape)
+    er, cnt = syn.check_sw_against_small(tiled, rhs.part, r0, wr)
+    ej, _ = syn.check_sw_against_small(tiled, rhs.part, jv, wj)
+    ej *= float(numpy.linalg.norm(wj)) / (dt * float(numpy.linalg.norm(wr)) / EPS_FD)
+    steps = max(5, min(args.steps, 20))
+    for _ in range(3):
+        rhs.jvp(v, dt, q, rhs(q))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        rhs.jvp(v, dt, q, rhs(q))
+    e1.record()
+    torch.cuda.synchronize()
+    hist, modes = rhs.timing_history(2 * steps)
+    nodes, n = tiled.num_nodes, tiled.n
+    peak, peak_src = measured_peaks()
+
+    def roof(tt, bpn, what):
+        sec = float(tt[:, 2].mean()) * 1e-3
+        ach = bpn * nodes / sec / 1e9
+        return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "kernels": [f"sw_traces<{n}>", f"sw_main<{n}>"],
+                "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
+                "algorithmic_bytes_per_node": bpn, "nodes_per_launch": nodes, "launches_timed": int(len(tt)), "what": what}
+
+    out = {
+        "workload": f"configs[1] galewsky shallow water: n={n}, {args.sw_nh}x{args.sw_nh} elements/panel x 6 panels (reference's 30x30 panel tiled)",
+        "nodes": nodes,
+        "dofs": 3 * nodes,
+        "value": 2.0 * 3 * nodes * steps / (e0.elapsed_time(e1) * 1e-3),
+        "unit": UNIT,
+        "ms_per_step": e0.elapsed_time(e1) / steps,
+        "roofline": roof(hist[modes < 0], 144 + 48 / n, "one shallow-water RHS evaluation"),
+        "roofline_jvp": roof(hist[modes >= 0], 192 + 48 / n, "one fused FD-JVP evaluation (cached base RHS)"),
+        "parity": {"rhs_rel_err": er, "jvp_err_over_dt_rhs_eps": ej, "elements_checked": cnt, "tolerance": 1e-12,
+                   "ok": bool(er <= 1e-12 and ej <= 1e-12)},
+    }
+    rhs.close()
+    return out
+
+
 def reference_line(args):
     """`--impl reference`: the CPU arm alone, on the arm's own config/metric/unit."""
     nh = args.nh if args.nh > 0 else nh_for(args.gpus, args.nh1)
@@ -486,6 +554,8 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=10)
     ap.add_argument("--skip-check", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-sw", action="store_true", help="skip the shallow-water side measurement (configs[1])")
+    ap.add_argument("--sw-nh", type=int, default=720, help="shallow-water elements per panel side")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: at least 3 warm-up steps
@@ -504,6 +574,8 @@ def main():
 
     line = run_b200(args)
     if rank == 0:
+        if args.gpus == 1 and not args.skip_sw:
+            line["shallow_water"] = run_shallow_water(args)
         if args.gpus == 1 and not args.skip_cpu:
             cpu = run_cpu_arm(args.cpu_steps, 2)
             line["cpu_baseline"] = {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port", "sample": cpu["sample"]}
