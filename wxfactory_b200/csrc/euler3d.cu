@@ -703,7 +703,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         const long long o = qo + v * vst;
         double x = r[v];
         if (JVP) {
-            x = a.dt * (x - r0[v]) / a.eps;
+            x = a.dt * (x - r0[v]) * a.inv_eps;  // matvec.py:66 divides by eps: same to one rounding
             if (a.mode == WXB_JVP_RAT) x = vv[v] - 0.5 * x;
         }
         a.out[o] = x;

@@ -209,10 +209,9 @@ __global__ void __launch_bounds__(Cfg2<N>::THREADS, Cfg2<N>::MINB) sw_main(const
         if (active) sw_make_info<N>(a, e, s_ei[le]);
         else s_ei[le].e = -1;
     }
-    if (active && node >= P - 4) {
-        const ElemPos ep = decode_elem(a.st, e, 1, a.nx, P, NVAR);
+    if (active && node >= P - 4) {  // one level: local column number == local element number
         const int f = node - (P - 4);
-        s_nr[le][f] = a.nbr[(long long)f * a.C + ep.c];
+        s_nr[le][f] = a.nbr[(long long)f * a.C + e];
     }
     __syncthreads();
 
@@ -272,8 +271,9 @@ __global__ void __launch_bounds__(Cfg2<N>::THREADS, Cfg2<N>::MINB) sw_main(const
 #pragma unroll
             for (int v = 0; v < NVAR; ++v) q[v] += a.eps * vv[v];
         }
-        u1 = q[1] / q[0];
-        u2 = q[2] / q[0];
+        const double ih = 1.0 / q[0];  // one reciprocal serves both velocities
+        u1 = q[1] * ih;
+        u2 = q[2] * ih;
         const double hsq = q[0] * q[0], hg = 0.5 * WXB_GRAVITY;
         const int col = le * P + node;
         s_f[0][col] = sg * q[1];
@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(Cfg2<N>::THREADS, Cfg2<N>::MINB) sw_main(const
     for (int v = 0; v < NVAR; ++v) {
         double x = r[v];
         if (JVP) {
-            x = a.dt * (x - r0[v]) / a.eps;
+            x = a.dt * (x - r0[v]) * a.inv_eps;  // matvec.py:66 divides by eps: same to one rounding
             if (a.mode == WXB_JVP_RAT) x = vv[v] - 0.5 * x;
         }
         a.out[qo + v * vst] = x;

@@ -185,6 +185,7 @@ void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, con
     a.q = q;
     a.v = v;
     a.eps = v ? eps : 0.0;
+    a.inv_eps = (v && eps != 0.0) ? 1.0 / eps : 0.0;
     a.rhs0 = rhs0;
     a.dt = dt;
     a.mode = mode;

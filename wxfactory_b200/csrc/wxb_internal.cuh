@@ -32,6 +32,7 @@ struct EvalArgs {
     const double* q;      // state
     const double* v;      // perturbation direction or nullptr
     double eps;           // q + eps*v
+    double inv_eps;       // 1/eps (0 when there is no direction): the JVP epilogue multiplies instead of dividing
     const double* rhs0;   // cached base RHS (JVP modes)
     double dt;
     int mode;             // -1 plain RHS, WXB_JVP_FD, WXB_JVP_RAT
