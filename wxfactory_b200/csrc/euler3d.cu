@@ -47,7 +47,7 @@
 #define WXB_MINB3 4
 #endif
 #ifndef WXB_MINB4
-#define WXB_MINB4 8
+#define WXB_MINB4 10
 #endif
 #ifndef WXB_MINB5
 #define WXB_MINB5 4
@@ -59,7 +59,7 @@
 #define WXB_CH3 0  // 1: Christoffel symbols loaded 9 at a time (fewer registers, less memory parallelism)
 #endif
 #ifndef WXB_MINB4
-#define WXB_MINB4 8
+#define WXB_MINB4 10
 #endif
 
 #ifndef WXB_RCP
