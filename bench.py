@@ -67,10 +67,10 @@ def b_jvp(n):
 
 # DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
 # of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
-# profiles/r01_v6_full_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
+# profiles/r01_final_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
 NCU_TRAFFIC_NODES = 10616832
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.424739e9 + 0.708382e9 + 4.544390e9 + 0.419160e9) / NCU_TRAFFIC_NODES,
-                        "jvp": (0.849587e9 + 1.134996e9 + 4.999879e9 + 0.424802e9) / NCU_TRAFFIC_NODES}
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.424687e9 + 0.710602e9 + 4.557608e9 + 0.444468e9) / NCU_TRAFFIC_NODES,
+                        "jvp": (0.849362e9 + 1.135007e9 + 5.014746e9 + 0.462132e9) / NCU_TRAFFIC_NODES}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -382,7 +382,7 @@ def run_b200(args):
                 "unit": "GB/s",
                 "frac": ach / peak,
                 "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
-                "traffic_source": "profiles/r01_v6_full_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
+                "traffic_source": "profiles/r01_final_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
                 "kernels": ["euler_traces<4>", "euler_main<4>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bytes_per_node,
@@ -450,6 +450,7 @@ def run_shallow_water(args):
     the reference's 30x30 panels tiled to --sw-nh.  Same protocol as the headline workload: device time of every
     evaluation from the C ABI's events, roofline against B_sw(n) = 144 + 48/n (RHS) / 192 + 48/n (JVP, + v and the
     cached base RHS) bytes per node, parity through the tiling periodicity against the numpy oracle."""
+    import numpy
     import torch
 
     from oracle import jvp_oracle
@@ -544,7 +545,7 @@ def reference_line(args):
 def main():
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--nz", type=int, default=12, help="elements per column")

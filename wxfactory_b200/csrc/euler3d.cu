@@ -62,6 +62,9 @@
 #define WXB_MINB4 10
 #endif
 
+#ifndef WXB_FR_MIN_N
+#define WXB_FR_MIN_N 4  // lowest order that builds the per-face address table in euler_main
+#endif
 #ifndef WXB_RCP
 #define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
 #endif
@@ -443,6 +446,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     using MC = MainCfg<N, STG>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
     constexpr bool STAGED = MC::STAGED;
+    constexpr bool USE_FR = N >= WXB_FR_MIN_N;  // per-face address table (direct mode)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     using SM = MainSmem<N, STG>;
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
@@ -458,7 +462,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     if (active && node == 0) make_info(a, e, F, P, sm.ei[le]);
     if (active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
-        if (STAGED) sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
+        if (STAGED || !USE_FR) sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
         else make_face_row(a, e, ep, node - (P - 6), F, sm.fr[le][node - (P - 6)]);
     }
     if (STAGED && threadIdx.x == 0) {
@@ -540,6 +544,21 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
 #pragma unroll
                 for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : sm.nb[f * NTR + v][le][pt2];  // mirrored ghost (rhs_dfr.py:265-268)
+            } else if (!USE_FR) {  // low orders: a face table per element costs more than it saves (few points per face)
+                const NbrRow& nr = sm.nr[le][f];
+                bc = nr.bc;
+                flags = nr.flags;
+                const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
+                const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
+                const long long cs = ei.fm_cs[d];
+                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+                const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
+                const double* src = bc ? t : a.trace + nr.row0 * F + pt2;  // mirrored ghost (rhs_dfr.py:265-268)
+                const long long vs = bc ? vs_own : nr.vs * F;
+#pragma unroll
+                for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
+#pragma unroll
+                for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
             } else {
                 const FaceRow& fr = sm.fr[le][f];
                 bc = fr.bc;
