@@ -491,12 +491,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         // serialisation); rows of consecutive elements are contiguous in global memory, so a run of elements moves
         // as one copy.
         if (threadIdx.x == 0) {
-            for (int el0 = 0; el0 < nact;) {  // runs of consecutive local element numbers (metric rows)
-                int L = 1;
-                while (el0 + L < nact && sm.ei[el0 + L].e == sm.ei[el0].e + L) ++L;
-                const double* src = a.chris + (long long)sm.ei[el0].e * P;
-                for (int row = R_CH; row < NROWS; ++row) bulk_g2s(&sm.st[row][el0][0], src + (long long)(row - R_CH) * EP, L * P * 8, &sm.bar[0]);
-                el0 += L;
+            for (int el = 0; el < nact; ++el) {  // the element's 35 metric rows are contiguous in global memory
+                const double* src = a.chris + (long long)sm.ei[el].e * (NMETRIC * P);
+                if (EB == 1) {
+                    bulk_g2s(&sm.st[R_CH][0][0], src, NMETRIC * P * 8, &sm.bar[0]);  // ... and in shared memory: one copy
+                } else {
+                    for (int row = R_CH; row < NROWS; ++row) bulk_g2s(&sm.st[row][el][0], src + (row - R_CH) * P, P * 8, &sm.bar[0]);
+                }
             }
             for (int el0 = 0; el0 < nact;) {  // ... and of consecutive state rows (same slab)
                 int L = 1;
@@ -597,17 +598,19 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         qo = ei.qoff + node;
         vst = ei.vstride;
         const long long mo = (long long)e * P + node;
+        // the element's metric block [35][P] (Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta): one base, constant offsets
+        const double* const mrow = a.chris + (long long)e * (NMETRIC * P) + node;
         double q[NVAR], h[6];
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) q[v] = STAGED ? col[(R_Q + v) * RS] : qsrc[qo + v * vst];
-        sg = STAGED ? col[R_SG * RS] : a.sqrtg[mo];
+        sg = STAGED ? col[R_SG * RS] : mrow[(R_SG - R_CH) * P];
 #pragma unroll
-        for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : a.h[c * EP + mo];
-        gfac = STAGED ? col[R_IDZ * RS] : a.idz[mo];
+        for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : mrow[(R_H - R_CH + c) * P];
+        gfac = STAGED ? col[R_IDZ * RS] : mrow[(R_IDZ - R_CH) * P];
         double ch[STAGED ? 1 : 27];  // direct mode: all 27 Christoffel loads in flight together
         if (!STAGED && !WXB_CH3) {
 #pragma unroll
-            for (int c = 0; c < 27; ++c) ch[c] = a.chris[c * EP + mo];
+            for (int c = 0; c < 27; ++c) ch[c] = mrow[c * P];
         }
         const double rho = q[0];
 #if WXB_RCP
@@ -627,7 +630,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 double c[9];
 #pragma unroll
                 for (int m = 0; m < 9; ++m)
-                    c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : (WXB_CH3 ? a.chris[(9 * i + m) * EP + mo] : ch[STAGED ? 0 : 9 * i + m]);
+                    c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : (WXB_CH3 ? mrow[(9 * i + m) * P] : ch[STAGED ? 0 : 9 * i + m]);
                 fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
                         c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
             }

@@ -105,21 +105,35 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     UP(h->d_ops, ops.data(), (size_t)nops);
 
     if (euler) {
-        // one contiguous block [35][E*P]: Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta, the row order in which
-        // euler_main stages an element (csrc/euler3d.cu): one base pointer + a row stride address all 35 rows
+        // one block, element-major: [E][35][P] with rows Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta.  A thread
+        // addresses all 35 values of its node with one base pointer and compile-time offsets, and an element's
+        // 35 rows (17.9 KB at n = 4) are one contiguous piece of HBM (one bulk copy in the TMA-staged variant).
         if (!A->sqrtg || !A->h || !A->chris || !A->inv_dzdeta) {
             set_err(h, "missing interior metric array");
             return WXB_EINVAL;
         }
         CU(cudaMalloc((void**)&h->d_metric, 35 * EP * sizeof(double)));
         h->d_chris = h->d_metric;
-        h->d_sqrtg = h->d_metric + 27 * EP;
-        h->d_h = h->d_metric + 28 * EP;
-        h->d_idz = h->d_metric + 34 * EP;
-        CU(cudaMemcpy(h->d_chris, A->chris, 27 * EP * sizeof(double), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(h->d_sqrtg, A->sqrtg, EP * sizeof(double), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(h->d_h, A->h, 6 * EP * sizeof(double), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(h->d_idz, A->inv_dzdeta, EP * sizeof(double), cudaMemcpyHostToDevice));
+        h->d_sqrtg = h->d_h = h->d_idz = nullptr;  // rows of the block, not separate arrays
+        {
+            double* tmp = nullptr;  // one host row [E*P] at a time, interleaved on the device
+            CU(cudaMalloc((void**)&tmp, EP * sizeof(double)));
+            const size_t rowb = (size_t)h->P * sizeof(double);
+            for (int r = 0; r < 35; ++r) {
+                const double* src = r < 27 ? A->chris + (size_t)r * EP
+                                  : r == 27 ? A->sqrtg
+                                  : r < 34 ? A->h + (size_t)(r - 28) * EP
+                                           : A->inv_dzdeta;
+                cudaError_t e1 = cudaMemcpy(tmp, src, EP * sizeof(double), cudaMemcpyHostToDevice);
+                cudaError_t e2 = e1 == cudaSuccess ? cudaMemcpy2D(h->d_metric + (size_t)r * h->P, 35 * rowb, tmp, rowb, rowb, (size_t)h->E, cudaMemcpyDeviceToDevice) : e1;
+                if (e2 != cudaSuccess) {
+                    cudaFree(tmp);
+                    set_err(h, "metric upload failed: %s", cudaGetErrorString(e2));
+                    return WXB_ECUDA;
+                }
+            }
+            cudaFree(tmp);
+        }
     } else {
         UP(h->d_sqrtg, A->sqrtg, EP);
         UP(h->d_h, A->h, 3 * EP);
