@@ -36,8 +36,9 @@ def test_slabs_cover_every_row_once():
             assert sorted(rows) == [(p, j) for p in range(6) for j in range(nh)]
 
 
+@pytest.mark.parametrize("layout", ["field", "element"])
 @pytest.mark.parametrize("nranks", [1, 2, 4, 8])
-def test_pull_tables_reproduce_reference_exchange(golden, nranks):
+def test_pull_tables_reproduce_reference_exchange(golden, nranks, layout):
     prob, ex = golden("dcmip31_n4")  # n=4, nz=4, nh=4
     n, nz, nh, F = prob.n, prob.nz, prob.nh, prob.F
     orc = EulerOracle(prob)
@@ -45,7 +46,7 @@ def test_pull_tables_reproduce_reference_exchange(golden, nranks):
     q = numpy.moveaxis(ex["Q0"], 1, 0) * (1.0 + 0.01 * rng.standard_normal((5,) + ex["Q0"].shape[:1] + ex["Q0"].shape[2:]))
     q_itf_x1, q_itf_x2 = q @ orc.extrap_x, q @ orc.extrap_y
     s_, n_, w_, e_ = orc._exchange(q_itf_x1, q_itf_x2)  # (5,6,nz,nh,F) each: the reference's received halos
-    parts = [pt.build_partition(nh, nz, n, prob.bnd_sn, prob.bnd_we, nranks, r) for r in range(nranks)]
+    parts = [pt.build_partition(nh, nz, n, prob.bnd_sn, prob.bnd_we, nranks, r, trace_layout=layout) for r in range(nranks)]
     traces = [emulate.local_traces(prob, p, q_itf_x1, q_itf_x2, 5, 6) for p in parts]
     emulate.exchange(parts, traces, 5, 6, nz, F)
     for p, tr in zip(parts, traces):

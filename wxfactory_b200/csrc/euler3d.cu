@@ -193,18 +193,17 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
     if (!active) return;
     // 3F lines per element; each yields the min-side and the max-side face value (same arithmetic per side as
     // extrap_line, which euler_main uses for the element's own side)
-    const long long fstride = (long long)a.E * F;  // one (field, face) plane of the trace array
     for (int ln = node; ln < 3 * F; ln += P) {
         const int d = ln / F, pt = ln % F;
         int base, step;
         line_of<N>(d, pt, base, step);
         double lo[NTR], hi[NTR];
         extrap_line2<N>(s_ext, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, lo, hi);
-        double* t = a.trace + ((long long)(2 * d) * a.E + e) * F + pt;
+        double* t = a.trace + (((long long)e * 6 + 2 * d) * NTR) * F + pt;  // [E][face][field][F]
 #pragma unroll
         for (int v = 0; v < NTR; ++v) {
-            t[v * 6 * fstride] = lo[v];
-            t[v * 6 * fstride + fstride] = hi[v];
+            t[v * F] = lo[v];
+            t[(NTR + v) * F] = hi[v];
         }
     }
 }
@@ -311,8 +310,8 @@ __device__ __forceinline__ NbrRow nbr_row(const EvalArgs& a, int e, int k, int c
     if (f >= 4) {
         r.bc = (f == 4) ? (k == 0) : (k == a.nz - 1);
         const int e2 = (f == 4) ? e - ny * a.nx : e + ny * a.nx;
-        r.row0 = (long long)(f ^ 1) * a.E + e2;
-        r.vs = 6LL * a.E;
+        r.row0 = ((long long)e2 * 6 + (f ^ 1)) * NTR;
+        r.vs = 1;
     } else {
         const int4 t = a.nbr[(long long)f * a.C + c];
         r.row0 = (long long)t.x + (long long)k * t.y;
@@ -336,9 +335,9 @@ __device__ __forceinline__ void make_face_row(const EvalArgs& a, int e, const El
     const NbrRow r = nbr_row(a, e, ep.k, ep.c, ep.ny, f);
     const int d = f >> 1, side = f & 1;
     const long long nz = a.nz, ny = ep.ny, nx = a.nx;
-    o.own = a.trace + ((long long)f * a.E + e) * F;
+    o.own = a.trace + (((long long)e * 6 + f) * NTR) * F;
     o.nb = r.bc ? o.own : a.trace + r.row0 * F;
-    o.nb_vs = r.bc ? 6LL * a.E * F : r.vs * F;
+    o.nb_vs = F;  // element-major trace layout: fields of a face are always one row apart (checked at create)
     o.flags = r.flags;
     o.bc = r.bc;
     if (d == 0) {
@@ -508,14 +507,14 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             }
         } else if (threadIdx.x == 32) {
             for (int f = 0; f < 6; ++f) {
-                for (int el0 = 0; el0 < nact;) {
-                    const NbrRow nr = sm.nr[el0][f];
-                    if (nr.bc) { ++el0; continue; }
-                    int L = 1;
-                    while (el0 + L < nact && !sm.nr[el0 + L][f].bc && sm.nr[el0 + L][f].row0 == nr.row0 + L && sm.nr[el0 + L][f].vs == nr.vs) ++L;
-                    for (int v = 0; v < NTR; ++v)
-                        bulk_g2s(&sm.nb[f * NTR + v][el0][0], a.trace + (nr.row0 + v * nr.vs) * F, L * F * 8, &sm.bar[1]);
-                    el0 += L;
+                for (int el = 0; el < nact; ++el) {  // the 6 fields of a facing face are contiguous in global memory
+                    const NbrRow nr = sm.nr[el][f];
+                    if (nr.bc) continue;
+                    if (EB == 1) {
+                        bulk_g2s(&sm.nb[f * NTR][0][0], a.trace + nr.row0 * F, NTR * F * 8, &sm.bar[1]);
+                    } else {
+                        for (int v = 0; v < NTR; ++v) bulk_g2s(&sm.nb[f * NTR + v][el][0], a.trace + (nr.row0 + v) * F, F * 8, &sm.bar[1]);
+                    }
                 }
             }
         }
@@ -525,7 +524,6 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     auto do_faces = [&]() {
         if (!active || (a.dbg & 1)) return;
         const ElemInfo& ei = sm.ei[le];
-        const long long vs_own = 6LL * a.E * F;
         for (int fp = node; fp < 6 * F; fp += P) {
             const int f = fp / F, pt = fp % F, d = f >> 1, side = f & 1;
             const int kl = pt / N, al = pt % N;
@@ -553,13 +551,12 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
                 const long long cs = ei.fm_cs[d];
                 fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
-                const double* t = a.trace + ((long long)f * a.E + ei.e) * F + pt;
+                const double* t = a.trace + (((long long)ei.e * 6 + f) * NTR) * F + pt;
                 const double* src = bc ? t : a.trace + nr.row0 * F + pt2;  // mirrored ghost (rhs_dfr.py:265-268)
-                const long long vs = bc ? vs_own : nr.vs * F;
 #pragma unroll
-                for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
+                for (int v = 0; v < NTR; ++v) own[v] = t[v * F];
 #pragma unroll
-                for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
+                for (int v = 0; v < NTR; ++v) nb[v] = src[v * F];
             } else {
                 const FaceRow& fr = sm.fr[le][f];
                 bc = fr.bc;
@@ -570,11 +567,10 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
                 const double* t = fr.own + pt;
                 const double* src = fr.nb + pt2;
-                const long long vs = fr.nb_vs;
 #pragma unroll
-                for (int v = 0; v < NTR; ++v) own[v] = t[v * vs_own];
+                for (int v = 0; v < NTR; ++v) own[v] = t[v * F];
 #pragma unroll
-                for (int v = 0; v < NTR; ++v) nb[v] = src[v * vs];
+                for (int v = 0; v < NTR; ++v) nb[v] = src[v * F];
             }
             apply_xform<N>(a, flags, al, nb);
             double res[7];
@@ -789,15 +785,23 @@ int wxb_euler_configure(int n) {
 }
 
 // pack the trace records other handles need: sendbuf[rec][var][k][F]
-__global__ void pack_kernel(const EvalArgs a, int nvar, int F, int nfaces) {
+__global__ void pack_kernel(const EvalArgs a, int nvar, int F, int nfaces, int elem_major) {
     const long long per_rec = (long long)nvar * a.nz * F;
     const long long total = per_rec * a.nsend;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         const int rec = (int)(t / per_rec);
         int r = (int)(t % per_rec);
-        const int v = r / (a.nz * F);
-        r %= a.nz * F;
-        const int k = r / F, pt = r % F;
+        int v, k;
+        if (elem_major) {  // record [k][field][F], the order of the element-major trace array
+            k = r / (nvar * F);
+            r %= nvar * F;
+            v = r / F;
+        } else {           // record [field][k][F]
+            v = r / (a.nz * F);
+            r %= a.nz * F;
+            k = r / F;
+        }
+        const int pt = r % F;
         const int cf = a.send[rec];
         const int c = cf >> 2, f = cf & 3;
         // column -> slab
@@ -806,16 +810,17 @@ __global__ void pack_kernel(const EvalArgs a, int nvar, int F, int nfaces) {
             if (c >= a.st.cbase[u]) s = u;
         const int cl = c - a.st.cbase[s];
         const int e = a.st.ebase[s] + k * a.st.ny[s] * a.nx + cl;
-        a.sendbuf[t] = a.trace[((long long)(v * nfaces + f) * a.E + e) * F + pt];
+        a.sendbuf[t] = elem_major ? a.trace[(((long long)e * nfaces + f) * nvar + v) * F + pt]
+                                  : a.trace[((long long)(v * nfaces + f) * a.E + e) * F + pt];
     }
 }
 
-int wxb_pack(const EvalArgs& a, int nvar, int F, int nfaces, cudaStream_t s) {
+int wxb_pack(const EvalArgs& a, int nvar, int F, int nfaces, int elem_major, cudaStream_t s) {
     if (a.nsend == 0) return 0;
     const long long total = (long long)a.nsend * nvar * a.nz * F;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    pack_kernel<<<blocks, 256, 0, s>>>(a, nvar, F, nfaces);
+    pack_kernel<<<blocks, 256, 0, s>>>(a, nvar, F, nfaces, elem_major);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

@@ -154,10 +154,18 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
         if (r != WXB_OK) return r;
         h->d_nbr = tmp;
     }
+    if (euler) {  // element-major trace layout: the fields of a facing row are one row apart (partition.py "element")
+        for (size_t t = 0; t < (size_t)4 * h->C; ++t)
+            if (A->nbr[t * 4 + 2] != 1) {
+                set_err(h, "Euler handles need the element-major trace layout (field stride 1 in the neighbour table, got %d)", A->nbr[t * 4 + 2]);
+                return WXB_EINVAL;
+            }
+    }
     UP(h->d_xform, A->xform, (size_t)cfg->nxform * n * 4);
     UP(h->d_send, A->send, (size_t)cfg->nsend);
 
-    // trace array: local part [ntr][nfaces][E][F], then ghost records [rec][ntr][nz][F]
+    // trace array: local part (SW [ntr][nfaces][E][F], Euler [E][nfaces][ntr][F]), then the ghost records
+    // (SW [rec][ntr][1][F], Euler [rec][nz][ntr][F]); the same number of doubles either way
     h->trace_local = (int64_t)h->ntr * h->nfaces * h->E * h->F;
     const int64_t ghost = (int64_t)cfg->nghost * h->ntr * nz * h->F;
     CU(cudaMalloc((void**)&h->d_trace, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
@@ -272,7 +280,7 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
     h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     CU(cudaEventRecord(h->ev[0], s));
     int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
-    if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, s);
+    if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, h->cfg.equations == WXB_EQ_EULER3D, s);
     if (r != 0) {
         set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;

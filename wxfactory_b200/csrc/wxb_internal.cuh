@@ -38,7 +38,7 @@ struct EvalArgs {
     int mode;             // -1 plain RHS, WXB_JVP_FD, WXB_JVP_RAT
     double* out;
     double* qp;           // scratch: q + eps*v (written by the traces kernel in JVP mode, read by the main kernel)
-    double* trace;        // [ntr][faces][E][F] then ghost records [rec][ntr][nz][F]  (ntr: Euler 6, SW 3)
+    double* trace;        // SW: [3][4][E][F] then ghost records [rec][3][1][F]; Euler: [E][6][6][F] then [rec][nz][6][F]
     double* sendbuf;
     const double* sqrtg;
     const double* h;
@@ -109,7 +109,7 @@ int wxb_euler_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_main(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_main(const EvalArgs& a, int n, cudaStream_t s);
-int wxb_pack(const EvalArgs& a, int ntr, int F, int nfaces, cudaStream_t s);
+int wxb_pack(const EvalArgs& a, int ntr, int F, int nfaces, int elem_major, cudaStream_t s);
 
 // decode a local element index into (slab, level k, local row jl, col i)
 struct ElemPos {

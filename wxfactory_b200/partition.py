@@ -120,6 +120,7 @@ class Partition:
     send_peers: list = field(default_factory=list)
     send: numpy.ndarray = None  # (nsend,) int32: local col*4 + face, in send-buffer order
     nghost: int = 0
+    trace_layout: str = "field"
 
     @property
     def nsend(self):
@@ -185,11 +186,21 @@ def _neighbour_column(p, j, i, face, nh):
     return _facing(p, NORTH, i, nh)
 
 
-def build_partition(nh, nz, n, bnd_sn, bnd_we, nranks=1, rank=0, num_var=5, nfaces=6):
+def build_partition(nh, nz, n, bnd_sn, bnd_we, nranks=1, rank=0, num_var=5, nfaces=6, trace_layout="field"):
     """bnd_sn / bnd_we: (6, nh*n) edge coordinates of every panel (problem.bnd_sn / bnd_we).
-    For shallow water pass nz=1, num_var=3, nfaces=4."""
+    For shallow water pass nz=1, num_var=3, nfaces=4.
+
+    trace_layout: how the device trace array is ordered, which fixes (base, kstride, vstride) of the pull table
+    (all in rows of F doubles):
+      "field"   [field][face][E] + ghost records [rec][field][k]       (shallow-water kernels)
+      "element" [E][face][field] + ghost records [rec][k][field]       (Euler kernels: an element's 36 rows and a
+                face's 6 fields are contiguous, the distance between fields is always one row)"""
+    if trace_layout not in ("field", "element"):
+        raise ValueError(f"unknown trace layout {trace_layout!r}")
+    elem_major = trace_layout == "element"
     slabs = slabs_of_rank(nh, nranks, rank)
     part = Partition(nh=nh, nz=nz, n=n, nranks=nranks, rank=rank, slabs=slabs)
+    part.trace_layout = trace_layout
     nx = nh
     # local numbering
     cbase, ebase, loc = [], [], {}
@@ -244,12 +255,17 @@ def build_partition(nh, nz, n, bnd_sn, bnd_we, nranks=1, rank=0, num_var=5, nfac
                     sq = local_slab(q, jq)
                     if sq >= 0:
                         slq = slabs[sq]
-                        base = fq * E + ebase[sq] + (jq - slq.j0) * nx + iq
-                        kstride, vstride = slq.ny * nx, nfaces * E
+                        e0 = ebase[sq] + (jq - slq.j0) * nx + iq  # the neighbour column's element at level 0
+                        if elem_major:
+                            base = (e0 * nfaces + fq) * num_var
+                            kstride, vstride = slq.ny * nx * nfaces * num_var, 1
+                        else:
+                            base = fq * E + e0
+                            kstride, vstride = slq.ny * nx, nfaces * E
                     else:
                         g = ghost_id[q, jq, iq, fq]
                         base = ghost_base + g * num_var * nz
-                        kstride, vstride = 1, nz
+                        kstride, vstride = (num_var, 1) if elem_major else (1, nz)
                     nbr[face, col] = (base, kstride, vstride, flags)
     part.nbr = nbr
     part.xform = numpy.stack(xrows) if xrows else numpy.zeros((0, n, 4))

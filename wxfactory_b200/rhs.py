@@ -67,6 +67,7 @@ class RhsB200:
             rank=self.rank,
             num_var=self.num_trace,
             nfaces=6 if euler else 4,
+            trace_layout="element" if euler else "field",  # what csrc/euler3d.cu / csrc/sw2d.cu index
         )
         self._lib = capi.load()
         cfg = capi.WxbConfig()
