@@ -215,7 +215,6 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
 struct ElemInfo {
     long long qoff, vstride;   // (var 0, this element, node 0) in the state; distance between variables
     const double* fm[3];       // (comp 0, min-side face, pt 0) of this element in fm_i / fm_j / fm_k
-    long long fm_cs[3];        // component stride of the slab's block
     long long fm_side[3];      // min-side -> max-side face
     int e, k, c, ny;
 };
@@ -229,15 +228,14 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
     o.c = ep.c;
     o.ny = ep.ny;
     const long long nz = a.nz, ny = ep.ny, nx = a.nx;
-    o.fm[0] = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i) * F;
-    o.fm_cs[0] = nz * ny * (nx + 1) * F;
-    o.fm_side[0] = F;
-    o.fm[1] = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl) * nx + ep.i) * F;
-    o.fm_cs[1] = nz * (ny + 1) * nx * F;
-    o.fm_side[1] = nx * F;
-    o.fm[2] = a.fmk + a.st.fmk[ep.s] + (((long long)ep.k * ny + ep.jl) * nx + ep.i) * F;
-    o.fm_cs[2] = (nz + 1) * ny * nx * F;
-    o.fm_side[2] = ny * nx * F;
+    // interface metric, face-major per slab: [face][4 components][F] (transposed at create, wxb_api.cu)
+    o.fm[0] = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i) * (4 * F);
+    o.fm_side[0] = 4 * F;
+    o.fm[1] = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl) * nx + ep.i) * (4 * F);
+    o.fm_side[1] = nx * (4 * F);
+    o.fm[2] = a.fmk + a.st.fmk[ep.s] + (((long long)ep.k * ny + ep.jl) * nx + ep.i) * (4 * F);
+    o.fm_side[2] = ny * nx * (4 * F);
+    (void)nz;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -328,7 +326,6 @@ struct FaceRow {
     const double* nb;   // facing side's field 0, point 0 (the own row again at a rigid boundary: mirrored ghost)
     const double* fm;   // interface metric, component 0, point 0
     long long nb_vs;    // distance between the facing row's fields
-    long long fm_cs;    // distance between interface-metric components
     int flags, bc;
 };
 __device__ __forceinline__ void make_face_row(const EvalArgs& a, int e, const ElemPos& ep, int f, int F, FaceRow& o) {
@@ -341,14 +338,11 @@ __device__ __forceinline__ void make_face_row(const EvalArgs& a, int e, const El
     o.flags = r.flags;
     o.bc = r.bc;
     if (d == 0) {
-        o.fm = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i + side) * F;
-        o.fm_cs = nz * ny * (nx + 1) * F;
+        o.fm = a.fmi + a.st.fmi[ep.s] + (((long long)ep.k * ny + ep.jl) * (nx + 1) + ep.i + side) * (4 * F);
     } else if (d == 1) {
-        o.fm = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl + side) * nx + ep.i) * F;
-        o.fm_cs = nz * (ny + 1) * nx * F;
+        o.fm = a.fmj + a.st.fmj[ep.s] + (((long long)ep.k * (ny + 1) + ep.jl + side) * nx + ep.i) * (4 * F);
     } else {
-        o.fm = a.fmk + a.st.fmk[ep.s] + ((((long long)ep.k + side) * ny + ep.jl) * nx + ep.i) * F;
-        o.fm_cs = (nz + 1) * ny * nx * F;
+        o.fm = a.fmk + a.st.fmk[ep.s] + ((((long long)ep.k + side) * ny + ep.jl) * nx + ep.i) * (4 * F);
     }
 }
 
@@ -536,8 +530,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 flags = nr.flags;
                 const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
                 const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
-                const long long cs = ei.fm_cs[d];
-                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+                fm[0] = m[0]; fm[1] = m[F]; fm[2] = m[2 * F]; fm[3] = m[3 * F];
                 int base, step;
                 line_of<N>(d, pt, base, step);
                 extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
@@ -549,8 +542,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 flags = nr.flags;
                 const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
                 const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
-                const long long cs = ei.fm_cs[d];
-                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+                fm[0] = m[0]; fm[1] = m[F]; fm[2] = m[2 * F]; fm[3] = m[3 * F];
                 const double* t = a.trace + (((long long)ei.e * 6 + f) * NTR) * F + pt;
                 const double* src = bc ? t : a.trace + nr.row0 * F + pt2;  // mirrored ghost (rhs_dfr.py:265-268)
 #pragma unroll
@@ -563,8 +555,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 flags = fr.flags;
                 const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
                 const double* m = fr.fm + pt;  // interface metric: 4 loads issued before anything depends on them
-                const long long cs = fr.fm_cs;
-                fm[0] = m[0]; fm[1] = m[cs]; fm[2] = m[2 * cs]; fm[3] = m[3 * cs];
+                fm[0] = m[0]; fm[1] = m[F]; fm[2] = m[2 * F]; fm[3] = m[3 * F];
                 const double* t = fr.own + pt;
                 const double* src = fr.nb + pt2;
 #pragma unroll

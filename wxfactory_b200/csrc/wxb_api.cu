@@ -148,6 +148,32 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     UP(h->d_fmi, A->fm_i, (size_t)oi);
     UP(h->d_fmj, A->fm_j, (size_t)oj);
     if (euler) UP(h->d_fmk, A->fm_k, (size_t)ok);
+    if (euler) {
+        // interface metric: the host hands [4 components][faces][F] per slab; euler_main reads the 4 components of
+        // a face point together, so each slab block is transposed once to [faces][4][F] (512 contiguous bytes per
+        // face at n = 4, component offsets known at compile time)
+        double* dirs[3] = {h->d_fmi, h->d_fmj, h->d_fmk};
+        const long long tot[3] = {oi, oj, ok};
+        for (int d = 0; d < 3; ++d) {
+            if (tot[d] == 0) continue;
+            double* tmp = nullptr;
+            CU(cudaMalloc((void**)&tmp, (size_t)tot[d] * sizeof(double)));
+            cudaError_t e1 = cudaMemcpy(tmp, dirs[d], (size_t)tot[d] * sizeof(double), cudaMemcpyDeviceToDevice);
+            for (int s = 0; s < cfg->nslabs && e1 == cudaSuccess; ++s) {
+                const long long ny = st.ny[s];
+                const long long nfaces = d == 0 ? (long long)nz * ny * (nx + 1) : d == 1 ? (long long)nz * (ny + 1) * nx : (long long)(nz + 1) * ny * nx;
+                const long long off = d == 0 ? st.fmi[s] : d == 1 ? st.fmj[s] : st.fmk[s];
+                const size_t rowb = (size_t)h->F * sizeof(double);
+                for (int c = 0; c < 4 && e1 == cudaSuccess; ++c)
+                    e1 = cudaMemcpy2D(dirs[d] + off + (size_t)c * h->F, 4 * rowb, tmp + off + (size_t)c * nfaces * h->F, rowb, rowb, (size_t)nfaces, cudaMemcpyDeviceToDevice);
+            }
+            cudaFree(tmp);
+            if (e1 != cudaSuccess) {
+                set_err(h, "interface metric transpose failed: %s", cudaGetErrorString(e1));
+                return WXB_ECUDA;
+            }
+        }
+    }
     {
         int4* tmp = nullptr;
         int r = upload(h, (int32_t**)&tmp, A->nbr, (size_t)4 * h->C * 4);
