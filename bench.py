@@ -69,8 +69,8 @@ def b_jvp(n):
 # of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
 # profiles/r01_final_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
 NCU_TRAFFIC_NODES = 10616832
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.424687e9 + 0.710602e9 + 4.557608e9 + 0.444468e9) / NCU_TRAFFIC_NODES,
-                        "jvp": (0.849362e9 + 1.135007e9 + 5.014746e9 + 0.462132e9) / NCU_TRAFFIC_NODES}
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.424807e9 + 0.708674e9 + 4.525539e9 + 0.430559e9) / NCU_TRAFFIC_NODES,
+                        "jvp": (0.849551e9 + 1.132855e9 + 4.988846e9 + 0.440028e9) / NCU_TRAFFIC_NODES}
 
 
 # ------------------------------------------------------------------------------------------------------------
