@@ -172,6 +172,51 @@ int wxb_timings(wxb_handle* h, float out_ms[3]);
  * per-call timestamp lists (wx_factory/rhs/rhs.py:78-79,190-213). */
 int wxb_timing_history(wxb_handle* h, int max_evals, float* out_ms, int* out_mode);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Per-step operators around the right-hand side (csrc/stepops.cu): the callers' side of the boundary.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* Per-step exponential modal filter of the 3-D state:  out = ((sqrtG q) @ expfilter_new) * inv_sqrtG
+ * <- DFROperators.apply_filter_3d (wx_factory/geometry/operators.py:257-261, applied once per step by
+ * wx_factory/simulation/simulation.py:148 when expfilter_apply = 1).  `filt` is the (n x n) nodal filter
+ * DFROperators.expfilter (operators.py:110-112, make_filter :215-237), row-major; the three 1-D passes replace the
+ * dense (n^3 x n^3) product.  out may alias q. */
+int wxb_set_expfilter(wxb_handle* h, const double* filt);
+int wxb_expfilter(wxb_handle* h, const double* q, double* out, void* stream);
+
+/* Vector algebra of the integrators and Krylov solvers on plain device arrays (no handle).  All asynchronous on
+ * `stream`; coefficient arrays are HOST pointers read before the call returns. */
+#define WXB_VEC_MAX_ROWS 64
+
+/* out = ((a x) + (b y)) + ((c z) dt), each operation rounded on its own: the bit pattern of numpy's
+ * a*x + b*y + c*z*dt  <- Tvdrk3.__step__ (wx_factory/integrators/tvdrk3.py:13-17), Ros2.__prestep__'s
+ * b = A(Q) + rhs*dt (wx_factory/integrators/ros2.py:30).  y may be NULL (term absent); a == 1 leaves x unscaled. */
+int wxb_vec_lincomb3(int64_t n, double a, const double* x, double b, const double* y, double c, const double* z, double dt,
+                     double* out, void* stream);
+
+/* *count_dev = number of non-finite entries  <- the NaN check of wx_factory/simulation/simulation.py:399-408 */
+int wxb_vec_nonfinite(int64_t n, const double* x, uint64_t* count_dev, void* stream);
+
+/* out_dev[i*k + c] = sum_x V[i*ldv + x] * W[c*ldw + x], i < m <= WXB_VEC_MAX_ROWS, k in {1, 2}
+ * <- V[ilow:j,:n] @ V[j,:n] and the norms of KIOPS (wx_factory/solvers/kiops.py:190-205), PMEX
+ * (wx_factory/solvers/pmex.py:150-230), Q[:j] @ Q[j-2:j].T of the 1-sync FGMRES (wx_factory/solvers/fgmres.py:38).
+ * Two-stage fixed-order reduction (bit-reproducible run to run); scratch_dev holds wxb_vec_multidot_scratch(m, k)
+ * doubles.  The result stays on the device: the caller all-reduces it over ranks (the reference's comm.allreduce,
+ * fgmres.py:41 / kiops.py:193) and reads it back -- the one synchronisation of the step. */
+int64_t wxb_vec_multidot_scratch(int m, int k);
+int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
+                     double* scratch_dev, void* stream);
+
+/* out = (b0 y + sum_{i<m} coef[i] V[i]) * s   <- V[j] - V[ilow:j].T @ H (kiops.py:199), V[j] / nrm (:208),
+ * beta * F[:j,0] @ V[:j,:n] (:278,286), x + Z.T @ y of FGMRES (fgmres.py:246-249).  y may be NULL; out may alias y. */
+int wxb_vec_combine(int64_t n, int m, const double* coef_host, const double* V, int64_t ldv, double b0, const double* y, double s,
+                    double* out, void* stream);
+
+/* The row updates of _ortho_1_sync_igs (wx_factory/solvers/fgmres.py:60-69) in one pass over the first m = j-2 rows:
+ * q2 -= Q[:m].T s2 ; q1 -= Q[:m].T s1 ; q2 /= norm ; q1 -= q2 r ; q1 /= norm   (q2 = Q[j-2], q1 = Q[j-1]). */
+int wxb_vec_gs1sync(int64_t n, int m, const double* s2_host, const double* s1_host, const double* Q, int64_t ldq, double norm,
+                    double r, double* q2, double* q1, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

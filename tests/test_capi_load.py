@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _declared():
     text = open(os.path.join(ROOT, "include", "wxb200.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(wxb_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(wxb_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_builds_and_exports_every_declared_symbol():

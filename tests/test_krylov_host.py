@@ -1,0 +1,54 @@
+"""Host logic of the device-resident Krylov solvers (wxfactory_b200/krylov.py) against the reference's own fgmres /
+kiops results on seeded small systems (tests/golden/krylov_small.npz, made by oracle/refharness/make_step_golden.py),
+with the CPU stand-in for the vector kernels (tests/vecops_cpu.py)."""
+
+import os
+
+import numpy
+import torch
+
+from vecops_cpu import CpuVecOps
+from wxfactory_b200.krylov import fgmres, kiops
+
+G = numpy.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "krylov_small.npz"))
+
+
+def _t(a):
+    return torch.from_numpy(numpy.ascontiguousarray(a, dtype=float))
+
+
+def test_fgmres_reproduces_reference_iterations_and_solution():
+    M = G["fg_M"]
+    A = lambda v: _t(M @ v.numpy())  # noqa: E731
+    for tag in ("a", "b"):
+        nr, nb, nit, flag, restart = G[f"fg_meta_{tag}"]
+        x, norm_r, norm_b, niter, fl, res = fgmres(A, _t(G["fg_b"]), x0=_t(G["fg_x0"]), tol=1e-10, restart=int(restart), maxiter=50, ops=CpuVecOps())
+        assert (niter, fl) == (int(nit), int(flag))
+        assert abs(norm_b - nb) <= 1e-13 * nb
+        want = G[f"fg_res_{tag}"]
+        got = numpy.array([r[0] for r in res])
+        assert got.shape == want.shape
+        # the history spans 10 decades; compare each entry relative to itself, loosely at the converged end
+        assert numpy.all(numpy.abs(got - want) <= 1e-6 * want + 1e-13)
+        assert numpy.linalg.norm(x.numpy() - G[f"fg_x_{tag}"]) <= 1e-12 * numpy.linalg.norm(G[f"fg_x_{tag}"])
+
+
+def test_fgmres_error_behaviour():
+    import pytest
+
+    with pytest.raises(ValueError):
+        fgmres(lambda v: v, _t(numpy.ones(5)), restart=20, ops=CpuVecOps())  # b shorter than the restart length
+    x, nr, nb, nit, flag, res = fgmres(lambda v: v, _t(numpy.zeros(50)), restart=5, ops=CpuVecOps())  # b = 0: immediate return
+    assert (nr, nb, nit, flag) == (0.0, 0.0, 0, 0) and float(x.abs().max()) == 0.0
+
+
+def test_kiops_reproduces_reference_substeps_and_result():
+    J = G["ki_J"]
+    A = lambda v: _t(J @ v.numpy())  # noqa: E731
+    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True))):
+        w, stats = kiops(taus, A, _t(G["ki_u"]), tol=1e-9, ops=CpuVecOps(), **kw)
+        want = G[f"ki_stats_{tag}"]
+        assert [int(stats[i]) for i in (0, 1, 2, 3, 5)] == [int(want[i]) for i in (0, 1, 2, 3, 5)]
+        assert abs(stats[4] - want[4]) <= 1e-3 * want[4]
+        ref = G[f"ki_w_{tag}"]
+        assert numpy.linalg.norm(w.numpy() - ref) <= 1e-11 * numpy.linalg.norm(ref)

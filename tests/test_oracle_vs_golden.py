@@ -45,3 +45,16 @@ def test_flat_input_shape_is_preserved(golden):
     out = orc.rhs(ex["Q0"].ravel())
     assert out.shape == (ex["Q0"].size,)
     assert rel(out, ex["rhs0"].ravel()) <= TOL
+
+
+@pytest.mark.parametrize("name", ["dcmip21", "dcmip21_n5", "dcmip31_n4"])
+def test_filter_oracle_matches_reference(golden, name):
+    import os
+
+    from conftest import GOLDEN
+    from oracle import filter_oracle
+
+    prob, ex = golden(name)
+    g = numpy.load(os.path.join(GOLDEN, f"expfilter_{name}.npz"))
+    out = filter_oracle.apply_filter_3d(prob, g["expfilter"], ex["Q0"])
+    assert rel(out, g["Qf"]) <= TOL

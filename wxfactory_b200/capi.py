@@ -63,6 +63,8 @@ class WxbStaticArrays(ctypes.Structure):
     _fields_ = _ARRAY_FIELDS
 
 
+WXB_VEC_MAX_ROWS = 64  # include/wxb200.h
+
 EXPORTS = [
     "wxb_version",
     "wxb_create",
@@ -84,6 +86,14 @@ EXPORTS = [
     "wxb_jvp_bound_host",
     "wxb_timings",
     "wxb_timing_history",
+    "wxb_set_expfilter",
+    "wxb_expfilter",
+    "wxb_vec_lincomb3",
+    "wxb_vec_nonfinite",
+    "wxb_vec_multidot_scratch",
+    "wxb_vec_multidot",
+    "wxb_vec_combine",
+    "wxb_vec_gs1sync",
 ]
 
 _lib = None
@@ -126,6 +136,15 @@ def load():
     lib.wxb_timings.argtypes = [vp, ctypes.POINTER(ctypes.c_float * 3)]
     lib.wxb_timing_history.argtypes = [vp, i32, vp, vp]
     lib.wxb_timing_history.restype = i32
+    lib.wxb_set_expfilter.argtypes = [vp, vp]
+    lib.wxb_expfilter.argtypes = [vp, vp, vp, vp]
+    lib.wxb_vec_lincomb3.argtypes = [i64, dbl, vp, dbl, vp, dbl, vp, dbl, vp, vp]
+    lib.wxb_vec_nonfinite.argtypes = [i64, vp, vp, vp]
+    lib.wxb_vec_multidot_scratch.argtypes = [i32, i32]
+    lib.wxb_vec_multidot_scratch.restype = i64
+    lib.wxb_vec_multidot.argtypes = [i64, i32, vp, i64, i32, vp, i64, vp, vp, vp]
+    lib.wxb_vec_combine.argtypes = [i64, i32, vp, vp, i64, dbl, vp, dbl, vp, vp]
+    lib.wxb_vec_gs1sync.argtypes = [i64, i32, vp, vp, vp, i64, dbl, dbl, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -69,10 +69,41 @@
 #define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
 #endif
 
+#ifndef WXB_TRACE_A
+#define WXB_TRACE_A 1  // trace fields (rho, u1, u2, w, rho theta, sound speed) and the log p lift folded into the
+                       // derivative matrix: no exp / reciprocal in the interface pass.  0: (rho, rho u, rho theta,
+                       // log rho theta) with the face pressure recomputed per face point
+#endif
+
 namespace {
 
 constexpr int NVAR = 5;
-constexpr int NTR = 6;  // trace fields: the 5 variables + log(rho*theta) as extrapolated (before the exp)
+// trace fields per face point.  WXB_TRACE_A: rho, u1, u2, w, rho*theta, a = sqrt(gamma p / rho) -- what the Rusanov
+// flux consumes, formed once per trace point here instead of once per side and per reader in euler_main.
+// Otherwise: the 5 variables + log(rho*theta) as extrapolated (before the exp).
+constexpr int NTR = 6;
+constexpr int NFF = WXB_TRACE_A ? 6 : 7;  // interface results per face point kept for the lift
+
+// extrapolated line sums -> the trace fields (l0 = log rho, l4 = log(rho theta), m1..m3 = momenta)
+__device__ __forceinline__ void trace_fields(double m1, double m2, double m3, double l0, double l4, double out[NTR]) {
+    const double rho = exp(l0);
+    out[0] = rho;
+    out[4] = exp(l4);
+#if WXB_TRACE_A
+    const double r = 1.0 / rho;
+    out[1] = m1 * r;
+    out[2] = m2 * r;
+    out[3] = m3 * r;
+    // a = sqrt(gamma p / rho) with p = p0*exp(gamma*log(Rd/p0 * rho_theta)) (pde_euler_cubesphere.py:158-160,
+    // fluxes.py:171-172) from the extrapolated logs with one exp and no sqrt: sqrt(gamma p0) exp((gamma(l4+c) - l0)/2)
+    out[5] = WXB_SQRT_GAMMA_P0 * exp(0.5 * (WXB_GAMMA * (l4 + WXB_LOG_RD_P0) - l0));
+#else
+    out[1] = m1;
+    out[2] = m2;
+    out[3] = m3;
+    out[5] = l4;
+#endif
+}
 
 template <int N>
 struct Cfg {
@@ -85,7 +116,10 @@ struct Cfg {
     static constexpr int MINB = (N == 2) ? WXB_MINB2 : (N == 3) ? WXB_MINB3 : (N == 4) ? WXB_MINB4 : (N == 5) ? WXB_MINB5 : WXB_MINB6;
     // offsets into the operator block
     static constexpr int O_DIFF = 2 * N, O_CORR = 2 * N + N * N, O_HF = 4 * N + N * N;
-    static constexpr int NOPS = 4 * N + 2 * N * N;
+    // derivative + lift of log p as ONE matrix acting on lg = log(Rd/p0 * rho theta) of the line, and the constant
+    // left over (built in extended precision at create, wxb_api.cu)
+    static constexpr int O_DLP = 4 * N + 2 * N * N, O_KLP = O_DLP + N * N;
+    static constexpr int NOPS = 5 * N + 3 * N * N;
 };
 
 __device__ __forceinline__ double pressure_of(double rho_theta) {
@@ -118,12 +152,7 @@ __device__ __forceinline__ void extrap_line(const double* __restrict__ ext, cons
         l0 = fma(w, lrho[o], l0);
         l4 = fma(w, lrt[o], l4);
     }
-    out[0] = exp(l0);
-    out[1] = a1;
-    out[2] = a2;
-    out[3] = a3;
-    out[4] = exp(l4);
-    out[5] = l4;
+    trace_fields(a1, a2, a3, l0, l4, out);
 }
 
 // both sides of one line at once (shares the loads); per side the same fma chain as extrap_line
@@ -142,8 +171,8 @@ __device__ __forceinline__ void extrap_line2(const double* __restrict__ ext, con
             b[v] = fma(wh, x[v], b[v]);
         }
     }
-    lo[0] = exp(a[3]); lo[1] = a[0]; lo[2] = a[1]; lo[3] = a[2]; lo[4] = exp(a[4]); lo[5] = a[4];
-    hi[0] = exp(b[3]); hi[1] = b[0]; hi[2] = b[1]; hi[3] = b[2]; hi[4] = exp(b[4]); hi[5] = b[4];
+    trace_fields(a[0], a[1], a[2], a[3], a[4], lo);
+    trace_fields(b[0], b[1], b[2], b[3], b[4], hi);
 }
 
 // line of face point pt of direction d: first node and node stride
@@ -191,6 +220,20 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
     }
     __syncthreads();
     if (!active) return;
+#if WXB_TRACE_A
+    // 6F trace points per element, one (line, side) per thread and round: all lanes of a warp carry a point (with both
+    // sides per thread the 3F lines fill only 3/4 of the block's lanes, and the per-point exp/reciprocal work dominates)
+    for (int tp = node; tp < 6 * F; tp += P) {
+        const int f = tp / F, pt = tp % F, d = f >> 1, side = f & 1;
+        int base, step;
+        line_of<N>(d, pt, base, step);
+        double o[NTR];
+        extrap_line<N>(s_ext + side * N, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, o);
+        double* t = a.trace + (((long long)e * 6 + f) * NTR) * F + pt;  // [E][face][field][F]
+#pragma unroll
+        for (int v = 0; v < NTR; ++v) t[v * F] = o[v];
+    }
+#else
     // 3F lines per element; each yields the min-side and the max-side face value (same arithmetic per side as
     // extrap_line, which euler_main uses for the element's own side)
     for (int ln = node; ln < 3 * F; ln += P) {
@@ -206,6 +249,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
             t[(NTR + v) * F] = hi[v];
         }
     }
+#endif
 }
 
 
@@ -243,6 +287,41 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
 //   own / nb : the 6 trace fields of this element's side and of the facing side (already flipped / rotated)
 //   out[0..3] = F* rows rho, rho u1, rho u2, rho theta ; out[4] = wflux_adv* ; out[5] = wflux_pres* (own side) ;
 //   out[6] = log(p_itf own side)                 (fluxes.py:150-222,326-403,507-582; rhs_dfr.py:106-139)
+#if WXB_TRACE_A
+// traces carry (rho, u1, u2, w, rho theta, a): momenta and pressure are products, the signal speed needs one sqrt of
+// the metric term; out[0..5] only (the own-side log p of the lift is folded into the derivative matrix, see O_DLP)
+template <int N>
+__device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
+                                              const double own[NTR], const double nb[NTR], const double fm[4], double out[NFF]) {
+    const double sg = fm[0], hd0 = fm[1], hd1 = fm[2], hd2 = fm[3];
+    const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
+    double L[NTR], R[NTR];
+#pragma unroll
+    for (int v = 0; v < NTR; ++v) {
+        L[v] = side ? own[v] : nb[v];
+        R[v] = side ? nb[v] : own[v];
+    }
+    double uL = d == 0 ? L[1] : (d == 1 ? L[2] : L[3]);
+    double uR = d == 0 ? R[1] : (d == 1 ? R[2] : R[3]);
+    if (bc) {  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
+        if (side == 0) uL = -uR; else uR = -uL;
+    }
+    constexpr double inv_gamma = 1.0 / WXB_GAMMA;
+    const double pL = L[5] * L[5] * (L[0] * inv_gamma), pR = R[5] * R[5] * (R[0] * inv_gamma);  // a^2 rho / gamma
+    const double sh = sqrt(hdd);
+    const double eig = fmax(fabs(uL) + sh * L[5], fabs(uR) + sh * R[5]);  // |u| + sqrt(h^dd gamma p / rho)
+    const double sguL = sg * uL, sguR = sg * uR, es = eig * sg;
+    const double mL1 = L[0] * L[1], mL2 = L[0] * L[2], mL3 = L[0] * L[3];
+    const double mR1 = R[0] * R[1], mR2 = R[0] * R[2], mR3 = R[0] * R[3];
+    out[0] = 0.5 * (sguL * L[0] + sguR * R[0] - es * (R[0] - L[0]));
+    out[1] = 0.5 * ((sguL * mL1 + sg * hd0 * pL) + (sguR * mR1 + sg * hd0 * pR) - es * (mR1 - mL1));
+    out[2] = 0.5 * ((sguL * mL2 + sg * hd1 * pL) + (sguR * mR2 + sg * hd1 * pR) - es * (mR2 - mL2));
+    out[3] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
+    out[4] = 0.5 * (sguL * mL3 + sguR * mR3 - es * (mR3 - mL3));
+    const double pown = side ? pL : pR;
+    out[5] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
+}
+#else
 template <int N>
 __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
                                               const double own[NTR], const double nb[NTR], const double fm[4], double out7[7]) {
@@ -293,6 +372,8 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     out7[5] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
     out7[6] = side ? lpL : lpR;  // log(p_itf) of the own side (rhs_dfr.py:113)
 }
+
+#endif
 
 // where the facing side's trace row (field 0, level of this element) starts, in units of F doubles; the distance
 // between fields; flags (bit0 = reversed along the edge, bits 8.. = 1 + xform row).  Vertical faces have no table.
@@ -408,8 +489,8 @@ struct MainCfg {
     static constexpr int RFL = STAGED ? R_FL : 0, RLOGP = RFL + 18, RSGRHO = RFL + 19;
     static constexpr int ROWS = STAGED ? NROWS : NFLUX;
     // interface results (6 faces x 7 values x F) reuse the dead rows when they fit
-    static constexpr bool FF_ALIAS = STAGED && (NROWS - R_FF) * P >= 42 * F;
-    static constexpr int FF_OWN = FF_ALIAS ? 1 : 42 * F;
+    static constexpr bool FF_ALIAS = STAGED && (NROWS - R_FF) * P >= 6 * NFF * F;
+    static constexpr int FF_OWN = FF_ALIAS ? 1 : 6 * NFF * F;
     static constexpr int NBR = STAGED ? 6 * NTR : 1, NBE = STAGED ? Cfg<N>::EB : 1, NBF = STAGED ? F : 1;
 };
 
@@ -564,10 +645,10 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
                 for (int v = 0; v < NTR; ++v) nb[v] = src[v * F];
             }
             apply_xform<N>(a, flags, al, nb);
-            double res[7];
+            double res[NFF];
             rusanov_point<N>(a, ei, d, side, pt, bc, own, nb, fm, res);
 #pragma unroll
-            for (int v = 0; v < 7; ++v) *ffp(f * 7 + v, pt) = res[v];
+            for (int v = 0; v < NFF; ++v) *ffp(f * NFF + v, pt) = res[v];
         }
     };
 
@@ -644,7 +725,11 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             fl[(d * 6 + 4) * RS] = sgu * q[3];
             fl[(d * 6 + 5) * RS] = sg * hd2;
         }
+#if WXB_TRACE_A
+        col[MC::RLOGP * RS] = lg;  // log p = log p0 + gamma*lg (pde_euler_cubesphere.py:124); see O_DLP
+#else
         col[MC::RLOGP * RS] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
+#endif
         col[MC::RSGRHO * RS] = sg * rho;
         if (STAGED) {  // for the element's own traces (phase 2)
             col[R_LRHO * RS] = log(rho);
@@ -685,13 +770,15 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const double dm = s_op[C::O_DIFF + idx * N + m];
 #pragma unroll
             for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * RS + m * step];
-            dv[6] += dm * slp[m * step];
+            dv[6] += (WXB_TRACE_A ? s_op[C::O_DLP + idx * N + m] : dm) * slp[m * step];
             if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[RS + m * step];
         }
         const double cw = s_op[C::O_CORR + idx * 2], ce = s_op[C::O_CORR + idx * 2 + 1];
         // the reference adds the lift to the derivative field by field, then combines (rhs_dfr.py:106-139)
 #pragma unroll
-        for (int v = 0; v < 7; ++v) dv[v] += cw * *ffp(2 * d * 7 + v, pt) + ce * *ffp((2 * d + 1) * 7 + v, pt);
+        for (int v = 0; v < NFF; ++v) dv[v] += cw * *ffp(2 * d * NFF + v, pt) + ce * *ffp((2 * d + 1) * NFF + v, pt);
+        // d(log p) + lift of the own-side face log p = gamma * (D + c_w (x) ext_w + c_e (x) ext_e) lg + const(idx)
+        if (WXB_TRACE_A) dv[6] = WXB_GAMMA * dv[6] + s_op[C::O_KLP + idx];
 #pragma unroll
         for (int v = 0; v < 4; ++v) acc[v] += dv[v];
         const double wpres = col[(MC::RFL + d * 6 + 5) * RS];

@@ -1,0 +1,339 @@
+// Per-step operators around the right-hand side -- sm_100a kernels, FP64, HBM-bound.
+//
+//   wxb_expfilter       per-step exponential modal filter  ((sqrtG Q) @ expfilter_new) * inv_sqrtG
+//                       wx_factory/geometry/operators.py:101-119,257-261 (applied by simulation.py:148), as three
+//                       sum-factorised 1-D passes in shared memory instead of the dense (P x P) GEMM
+//   wxb_vec_lincomb3    ((a x) + (b y)) + ((c z) dt): the stage combinations of SSP-RK3
+//                       (wx_factory/integrators/tvdrk3.py:13-17) and Ros2's b = A(Q) + rhs dt
+//                       (wx_factory/integrators/ros2.py:30), rounded operation by operation like the numpy expressions
+//   wxb_vec_nonfinite   the NaN check of simulation.py:399-408
+//   wxb_vec_multidot    out[i][c] = V[i] . W[c]: the Gram-Schmidt products of KIOPS (wx_factory/solvers/kiops.py:190-197,
+//                       201-205), PMEX (wx_factory/solvers/pmex.py:150-230) and of the 1-sync FGMRES
+//                       (wx_factory/solvers/fgmres.py:38); fixed-order two-stage reduction (bit-reproducible run to run)
+//   wxb_vec_combine     out = (b0 y + sum_i c[i] V[i]) * s: kiops.py:199,208,278,286 / Krylov solution updates
+//   wxb_vec_gs1sync     the row updates of fgmres.py:60-69 (_ortho_1_sync_igs) in one pass over the basis
+//
+// The vector kernels are free functions of the C ABI (no handle): Krylov vectors are plain device arrays.
+#include <cstdarg>
+#include <cstdio>
+
+#include "wxb_internal.cuh"
+
+namespace {
+
+void set_err(wxb_handle* h, const char* fmt, ...) {  // same convention as wxb_api.cu: message kept on the handle
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(h->err, sizeof(h->err), fmt, ap);
+    va_end(ap);
+}
+
+constexpr int VEC_THREADS = 256;
+constexpr int VEC_BLOCKS = 148 * 4;  // persistent grid-stride blocks: a multiple of the SM count
+constexpr int MD_ROWS = 8;           // basis rows per pass of the multi-dot kernel (register accumulators)
+
+// ------------------------------------------------------------------------------------------------------
+// exponential filter: one thread per node and variable pass; element fields staged in shared memory
+template <int N>
+__global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_kernel(const EvalArgs a, const double* __restrict__ filt,
+                                                                                   const double* __restrict__ metric) {
+    constexpr int P = N * N * N, NV = 5;
+    constexpr int EB = P <= 64 ? 256 / P : 1;  // elements per block
+    __shared__ double s_f[N * N];
+    __shared__ double s_a[EB][NV][P];
+    __shared__ double s_b[EB][NV][P];
+    const int le = threadIdx.x / P, node = threadIdx.x % P;
+    const int e = blockIdx.x * EB + le;
+    const bool active = le < EB && e < a.E;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) s_f[t] = filt[t];
+    double sg = 1.0;
+    long long qo = 0, vst = 0;
+    if (active) {
+        const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NV);
+        qo = ep.qoff + node;
+        vst = ep.vstride;
+        sg = metric[(long long)e * (35 * P) + 27 * P + node];  // row sqrtG of the element-major metric block
+        double x[NV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) x[v] = a.q[qo + v * vst];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) s_a[le][v][node] = sg * x[v];
+    }
+    __syncthreads();
+    const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
+    // expfilter_new = (filter_x @ filter_y) @ filter_z with filter_d = kron(.., expfilter, ..).T: the passes commute
+    // in exact arithmetic; x, y, z is the order of the reference's product (operators.py:115-119)
+    if (active) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+#pragma unroll
+            for (int m = 0; m < N; ++m) s = fma(s_f[ii * N + m], s_a[le][v][node - ii + m], s);
+            s_b[le][v][node] = s;
+        }
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+#pragma unroll
+            for (int m = 0; m < N; ++m) s = fma(s_f[jj * N + m], s_b[le][v][node + (m - jj) * N], s);
+            s_a[le][v][node] = s;
+        }
+    }
+    __syncthreads();
+    if (active) {
+        const double inv = 1.0 / sg;  // metric.inv_sqrtG_new (metric3d.py:1157)
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+#pragma unroll
+            for (int m = 0; m < N; ++m) s = fma(s_f[kk * N + m], s_a[le][v][node + (m - kk) * N * N], s);
+            a.out[qo + v * vst] = s * inv;
+        }
+    }
+}
+
+template <int N>
+int launch_expfilter(const EvalArgs& a, const double* filt, const double* metric, cudaStream_t s) {
+    constexpr int P = N * N * N;
+    constexpr int EB = P <= 64 ? 256 / P : 1;
+    constexpr int threads = P <= 64 ? 256 : P;
+    expfilter_kernel<N><<<(a.E + EB - 1) / EB, threads, 0, s>>>(a, filt, metric);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// ((a x) + (b y)) + ((c z) dt), every operation rounded on its own (no fused multiply-add), so that the result is
+// the bit pattern numpy produces for  a*x + b*y + c*z*dt  evaluated left to right.  y == nullptr: (a x) + ((c z) dt).
+__global__ void __launch_bounds__(VEC_THREADS) lincomb3_kernel(long long n, double ca, const double* __restrict__ x, double cb,
+                                                              const double* __restrict__ y, double cc,
+                                                              const double* __restrict__ z, double dt, double* __restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += stride) {
+        double s = ca == 1.0 ? x[i] : __dmul_rn(ca, x[i]);
+        if (y) s = __dadd_rn(s, __dmul_rn(cb, y[i]));
+        out[i] = __dadd_rn(s, __dmul_rn(__dmul_rn(cc, z[i]), dt));
+    }
+}
+
+__global__ void __launch_bounds__(VEC_THREADS) nonfinite_kernel(long long n, const double* __restrict__ x, unsigned long long* count) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned int bad = 0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += stride) bad += !isfinite(x[i]);
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(count, (unsigned long long)bad);  // integer count: order-independent
+}
+
+// ------------------------------------------------------------------------------------------------------
+// multi-dot, stage 1: partial[block][i][c] = sum over the block's grid-stride entries of V[i][x] W[c][x]
+// (m <= MD_ROWS rows per launch, K = 1 or 2 right-hand vectors); warp-shuffle + shared-memory reduction in a fixed order
+template <int K>
+__global__ void __launch_bounds__(VEC_THREADS) multidot_partial(long long n, int m, const double* __restrict__ V, long long ldv,
+                                                               const double* __restrict__ W, long long ldw, double* __restrict__ partial,
+                                                               int mtot, int row0) {
+    double acc[MD_ROWS][K];
+#pragma unroll
+    for (int i = 0; i < MD_ROWS; ++i)
+#pragma unroll
+        for (int c = 0; c < K; ++c) acc[i][c] = 0.0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
+        double w[K];
+#pragma unroll
+        for (int c = 0; c < K; ++c) w[c] = W[c * ldw + x];
+#pragma unroll
+        for (int i = 0; i < MD_ROWS; ++i) {
+            if (i < m) {
+                const double v = V[i * ldv + x];
+#pragma unroll
+                for (int c = 0; c < K; ++c) acc[i][c] = fma(v, w[c], acc[i][c]);
+            }
+        }
+    }
+    __shared__ double s_red[VEC_THREADS / 32][MD_ROWS][K];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < MD_ROWS; ++i)
+#pragma unroll
+        for (int c = 0; c < K; ++c) {
+            double v = acc[i][c];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            if (lane == 0) s_red[warp][i][c] = v;
+        }
+    __syncthreads();
+    if (threadIdx.x < MD_ROWS * K) {
+        const int i = threadIdx.x / K, c = threadIdx.x % K;
+        if (i < m) {
+            double v = 0.0;
+#pragma unroll
+            for (int wgt = 0; wgt < VEC_THREADS / 32; ++wgt) v += s_red[wgt][i][c];
+            partial[((long long)blockIdx.x * mtot + row0 + i) * K + c] = v;
+        }
+    }
+}
+
+// stage 2: out[i][c] = sum over blocks, in block order
+__global__ void multidot_final(int nblocks, int mk, const double* __restrict__ partial, double* __restrict__ out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= mk) return;
+    double v = 0.0;
+    for (int b = 0; b < nblocks; ++b) v += partial[(long long)b * mk + t];
+    out[t] = v;
+}
+
+struct Coefs {
+    double c[WXB_VEC_MAX_ROWS];
+};
+
+// out = (b0 y + sum_i c[i] V[i]) * s   (y may be null; out may alias y or a row of V that is not summed over)
+__global__ void __launch_bounds__(VEC_THREADS) combine_kernel(long long n, int m, const Coefs cf, const double* __restrict__ V, long long ldv,
+                                                             double b0, const double* y, double s, double* out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
+        double acc = 0.0;
+        for (int i = 0; i < m; ++i) acc = fma(cf.c[i], V[i * ldv + x], acc);
+        if (y) acc = b0 * y[x] + acc;
+        out[x] = acc * s;
+    }
+}
+
+// rows j-2 and j-1 of the 1-sync Gram-Schmidt (fgmres.py:60-69), m = j-2 earlier rows:
+//   q2 -= sum_i Q[i] s2[i] ; q1 -= sum_i Q[i] s1[i] ; q2 /= norm ; q1 -= q2 r ; q1 /= norm
+__global__ void __launch_bounds__(VEC_THREADS) gs1sync_kernel(long long n, int m, const Coefs s2, const Coefs s1, const double* __restrict__ Q,
+                                                             long long ldq, double norm, double r, double* q2, double* q1) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
+        double a2 = 0.0, a1 = 0.0;
+        for (int i = 0; i < m; ++i) {
+            const double v = Q[i * ldq + x];
+            a2 = fma(v, s2.c[i], a2);
+            a1 = fma(v, s1.c[i], a1);
+        }
+        const double v2 = (q2[x] - a2) / norm;
+        q2[x] = v2;
+        q1[x] = (q1[x] - a1 - v2 * r) / norm;
+    }
+}
+
+int grid_for(long long n) {
+    long long b = (n + VEC_THREADS - 1) / VEC_THREADS;
+    return (int)(b < VEC_BLOCKS ? (b > 0 ? b : 1) : VEC_BLOCKS);
+}
+
+}  // namespace
+
+extern "C" {
+
+int wxb_set_expfilter(wxb_handle* h, const double* filt) {
+    if (!h) return WXB_EINVAL;
+    if (h->cfg.equations != WXB_EQ_EULER3D || !filt) {
+        set_err(h, "the exponential filter applies to 3-D Euler handles and needs the (n x n) nodal filter");
+        return WXB_EINVAL;
+    }
+    cudaSetDevice(h->device);
+    if (!h->d_expf && cudaMalloc((void**)&h->d_expf, (size_t)h->n * h->n * sizeof(double)) != cudaSuccess) {
+        set_err(h, "cudaMalloc of the filter failed");
+        return WXB_ENOMEM;
+    }
+    if (cudaMemcpy(h->d_expf, filt, (size_t)h->n * h->n * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_err(h, "filter upload failed");
+        return WXB_ECUDA;
+    }
+    return WXB_OK;
+}
+
+int wxb_expfilter(wxb_handle* h, const double* q, double* out, void* stream) {
+    if (!h) return WXB_EINVAL;
+    if (!h->d_expf) {
+        set_err(h, "wxb_expfilter called before wxb_set_expfilter");
+        return WXB_ESTATE;
+    }
+    if (!q || !out) {
+        set_err(h, "null state/output pointer");
+        return WXB_EINVAL;
+    }
+    cudaSetDevice(h->device);
+    EvalArgs a{};
+    a.q = q;
+    a.out = out;
+    a.E = h->E;
+    a.nz = h->cfg.nz;
+    a.nx = h->cfg.nx;
+    a.st = h->st;
+    cudaStream_t s = (cudaStream_t)stream;
+    int r = -1;
+    switch (h->n) {
+        case 2: r = launch_expfilter<2>(a, h->d_expf, h->d_metric, s); break;
+        case 3: r = launch_expfilter<3>(a, h->d_expf, h->d_metric, s); break;
+        case 4: r = launch_expfilter<4>(a, h->d_expf, h->d_metric, s); break;
+        case 5: r = launch_expfilter<5>(a, h->d_expf, h->d_metric, s); break;
+        case 6: r = launch_expfilter<6>(a, h->d_expf, h->d_metric, s); break;
+    }
+    if (r != 0) {
+        set_err(h, "filter kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return WXB_ECUDA;
+    }
+    return WXB_OK;
+}
+
+int wxb_vec_lincomb3(int64_t n, double a, const double* x, double b, const double* y, double c, const double* z, double dt,
+                     double* out, void* stream) {
+    if (n < 0 || !x || !z || !out) return WXB_EINVAL;
+    if (n == 0) return WXB_OK;
+    lincomb3_kernel<<<grid_for(n), VEC_THREADS, 0, (cudaStream_t)stream>>>(n, a, x, b, y, c, z, dt, out);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+int wxb_vec_nonfinite(int64_t n, const double* x, uint64_t* count_dev, void* stream) {
+    if (n < 0 || !x || !count_dev) return WXB_EINVAL;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaMemsetAsync(count_dev, 0, sizeof(uint64_t), s) != cudaSuccess) return WXB_ECUDA;
+    if (n == 0) return WXB_OK;
+    nonfinite_kernel<<<grid_for(n), VEC_THREADS, 0, s>>>(n, x, (unsigned long long*)count_dev);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+int64_t wxb_vec_multidot_scratch(int m, int k) { return (int64_t)VEC_BLOCKS * m * k; }
+
+int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
+                     double* scratch_dev, void* stream) {
+    if (n <= 0 || m <= 0 || m > WXB_VEC_MAX_ROWS || (k != 1 && k != 2) || !V || !W || !out_dev || !scratch_dev) return WXB_EINVAL;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int blocks = grid_for(n);
+    for (int row0 = 0; row0 < m; row0 += MD_ROWS) {
+        const int mm = m - row0 < MD_ROWS ? m - row0 : MD_ROWS;
+        if (k == 1)
+            multidot_partial<1><<<blocks, VEC_THREADS, 0, s>>>(n, mm, V + row0 * ldv, ldv, W, ldw, scratch_dev, m, row0);
+        else
+            multidot_partial<2><<<blocks, VEC_THREADS, 0, s>>>(n, mm, V + row0 * ldv, ldv, W, ldw, scratch_dev, m, row0);
+    }
+    multidot_final<<<(m * k + 127) / 128, 128, 0, s>>>(blocks, m * k, scratch_dev, out_dev);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+int wxb_vec_combine(int64_t n, int m, const double* coef_host, const double* V, int64_t ldv, double b0, const double* y, double s,
+                    double* out, void* stream) {
+    if (n < 0 || m < 0 || m > WXB_VEC_MAX_ROWS || (m > 0 && (!coef_host || !V)) || !out) return WXB_EINVAL;
+    if (n == 0) return WXB_OK;
+    Coefs cf;
+    for (int i = 0; i < m; ++i) cf.c[i] = coef_host[i];
+    combine_kernel<<<grid_for(n), VEC_THREADS, 0, (cudaStream_t)stream>>>(n, m, cf, V, ldv, b0, y, s, out);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+int wxb_vec_gs1sync(int64_t n, int m, const double* s2_host, const double* s1_host, const double* Q, int64_t ldq, double norm,
+                    double r, double* q2, double* q1, void* stream) {
+    if (n <= 0 || m < 0 || m > WXB_VEC_MAX_ROWS || (m > 0 && (!s2_host || !s1_host || !Q)) || !q2 || !q1 || norm == 0.0) return WXB_EINVAL;
+    Coefs c2, c1;
+    for (int i = 0; i < m; ++i) {
+        c2.c[i] = s2_host[i];
+        c1.c[i] = s1_host[i];
+    }
+    gs1sync_kernel<<<grid_for(n), VEC_THREADS, 0, (cudaStream_t)stream>>>(n, m, c2, c1, Q, ldq, norm, r, q2, q1);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+}  // extern "C"

@@ -1,4 +1,5 @@
 // C ABI of libwxb200.so (see include/wxb200.h for the contract and the reference interfaces replaced).
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -91,7 +92,7 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     h->C = cb;
     const size_t EP = (size_t)h->E * h->P;
 
-    const int nops = euler ? 4 * n + 2 * n * n : 4 * n + n * n;
+    const int nops = euler ? 5 * n + 3 * n * n : 4 * n + n * n;
     std::vector<double> ops(nops, 0.0);
     if (!A->ext_w || !A->ext_e || !A->diff || !A->corr || (euler && !A->hfilt)) {
         set_err(h, "missing operator block");
@@ -101,7 +102,33 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     memcpy(&ops[n], A->ext_e, n * sizeof(double));
     memcpy(&ops[2 * n], A->diff, n * n * sizeof(double));
     memcpy(&ops[2 * n + n * n], A->corr, 2 * n * sizeof(double));
-    if (euler) memcpy(&ops[4 * n + n * n], A->hfilt, n * n * sizeof(double));
+    if (euler) {
+        memcpy(&ops[4 * n + n * n], A->hfilt, n * n * sizeof(double));
+        // The reference differentiates log p = log p0 + gamma*lg (lg = log(Rd/p0 * rho theta)) at the nodes and lifts
+        // the own-side face value log p0 + gamma*(sum_m ext[m] log(rho theta)_m + log(Rd/p0)) (rhs_dfr.py:106-139,
+        // pde_euler_cubesphere.py:124,158-160).  Both are linear in the line's lg values, so the kernel applies ONE
+        // matrix  M = D + c_w (x) ext_w + c_e (x) ext_e  to lg and adds the constant that the float64 operator
+        // entries leave over (rows of D + corrections do not sum to exactly 0, extrapolation rows not to exactly 1):
+        //   K[i] = log p0 * (sum_m D[i][m] + c_w[i] + c_e[i]) + gamma*log(Rd/p0) * (c_w[i](1 - sum ext_w) + c_e[i](1 - sum ext_e))
+        // formed here in extended precision, i.e. the exactly-rounded value of what the reference's formulas define.
+        const long double lp0 = logl(100000.0L), lrd = logl(287.05L / 100000.0L), gam = (long double)(double)WXB_GAMMA;
+        long double sw = 0.0L, se = 0.0L;
+        for (int m = 0; m < n; ++m) {
+            sw += (long double)A->ext_w[m];
+            se += (long double)A->ext_e[m];
+        }
+        double* M = &ops[4 * n + 2 * n * n];
+        double* K = M + n * n;
+        for (int i = 0; i < n; ++i) {
+            const long double cw = A->corr[2 * i], ce = A->corr[2 * i + 1];
+            long double rs = cw + ce;
+            for (int m = 0; m < n; ++m) {
+                rs += (long double)A->diff[i * n + m];
+                M[i * n + m] = (double)((long double)A->diff[i * n + m] + cw * (long double)A->ext_w[m] + ce * (long double)A->ext_e[m]);
+            }
+            K[i] = (double)(lp0 * rs + gam * lrd * (cw * (1.0L - sw) + ce * (1.0L - se)));
+        }
+    }
     UP(h->d_ops, ops.data(), (size_t)nops);
 
     if (euler) {
@@ -421,7 +448,7 @@ int wxb_destroy(wxb_handle* h) {
     void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
                     h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf, h->d_qp,  h->d_q,           h->d_v,
-                    h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist};
+                    h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist, h->d_expf};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int r = 0; r < WXB_TIMING_RING; ++r)

@@ -14,6 +14,7 @@
 #define WXB_GAMMA (WXB_CPD / WXB_CVD)
 #define WXB_LOG_RD_P0 (-5.853269048356583)  // log(Rd / p0), correctly rounded
 #define WXB_LOG_P0 11.512925464970229      // log(p0)
+#define WXB_SQRT_GAMMA_P0 374.10732733784823  // sqrt((cpd/cvd) * p0), correctly rounded
 
 #define WXB_TIMING_RING 256
 
@@ -53,7 +54,7 @@ struct EvalArgs {
     const int4* nbr;
     const double* xform;
     const int* send;
-    const double* ops;    // ext_w[n] ext_e[n] diff[n*n] corr[2n] hfilt[n*n]
+    const double* ops;    // ext_w[n] ext_e[n] diff[n*n] corr[2n] hfilt[n*n] (Euler: + dlogp[n*n] klogp[n], wxb_api.cu)
     const int* elist;     // optional list of elements to process (nullptr = all)
     int nelist;
     int E, C, nz, nx, nsend;
@@ -75,6 +76,7 @@ struct wxb_handle {
     // device arrays
     double* d_metric;  // Euler: owner of d_chris / d_sqrtg / d_h / d_idz (one block, see wxb_api.cu)
     double *d_ops, *d_sqrtg, *d_h, *d_chris, *d_idz, *d_damp, *d_topo, *d_fmi, *d_fmj, *d_fmk, *d_topo_itf, *d_xform;
+    double* d_expf;    // (n x n) nodal exponential filter (wxb_set_expfilter), stepops.cu
     int4* d_nbr;
     int *d_send, *d_elist_inner, *d_elist_outer;
     int n_inner, n_outer;
