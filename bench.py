@@ -438,11 +438,93 @@ def run_b200(args):
             "parity": parity,
             "setup_s": t_setup,
         }
+    if world == 1 and line is not None and not args.skip_stepops:
+        line["stepops"] = measure_stepops(rhs, q_d, rhs0_d, peak)
     rhs.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return line
+
+
+def measure_stepops(rhs, q_d, r_d, peak, reps=10):
+    """Side measurement: the per-step kernels of csrc/stepops.cu at the bench size, each timed
+    with CUDA events over `reps` launches after 3 warm-up launches, as algorithmic bytes / time against the measured HBM
+    peak, with the numpy expression the reference evaluates timed beside it on one host core on a 1/16 sample.
+    Inputs (0.42 GB state, 8.9 GB Krylov basis) are larger than L2."""
+    import numpy
+    import torch
+
+    from wxfactory_b200.stepops import ExpFilterB200, VecOps
+
+    ops = VecOps(rhs.device_index)
+    n = q_d.numel()
+    reps = int(os.environ.get("WXB_STEPOPS_REPS", reps))  # 1 under ncu: every kernel captured once
+    out = {"state_values": n, "reps": reps}
+
+    def timed(fn):
+        for _ in range(3 if reps > 1 else 0):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    def cpu_timed(fn):
+        fn()
+        t0 = time.perf_counter()
+        fn()
+        return (time.perf_counter() - t0) * 1e3
+
+    def entry(ms, nbytes, cpu_ms, cpu_frac, note):
+        ach = nbytes / (ms * 1e-3) / 1e9
+        return {"ms": ms, "bytes": nbytes, "achieved_gbs": ach, "frac_of_hbm_peak": ach / peak,
+                "cpu_numpy_ms_scaled": cpu_ms / cpu_frac, "cpu_sample": f"1/{int(1 / cpu_frac)} of the vectors, 1 core", "what": note}
+
+    ns = n // 16
+    xs, ys, zs = (numpy.random.default_rng(i).standard_normal(ns) for i in range(3))
+    # exponential filter: read 5 variables + sqrtG, write 5 (88 B per node)
+    P = rhs.prob.n ** 3
+    F1 = numpy.eye(rhs.prob.n) * 0.9 + 0.1 / rhs.prob.n
+    filt = ExpFilterB200(rhs, F1)
+    ms = timed(lambda: filt(q_d))
+    dense = numpy.kron(numpy.kron(F1, F1), F1)
+    qs = xs[: (ns // (5 * P)) * 5 * P].reshape(5, -1, P)
+    sgs = numpy.abs(ys[: qs.shape[1] * P]).reshape(1, -1, P) + 1.0
+    out["expfilter"] = entry(ms, (n + n + n // 5) * 8, cpu_timed(lambda: ((sgs * qs) @ dense) * (1.0 / sgs)), qs.size / n,
+                             "wxb_expfilter: ((sqrtG Q) @ expfilter_new) * inv_sqrtG as three 1-D passes")
+    # SSP-RK3 stage combination: 3 reads + 1 write
+    tmp = torch.empty_like(q_d)
+    ms = timed(lambda: ops.lincomb3(0.75, q_d, 0.25, r_d, 0.25, r_d, 0.5, out=tmp))
+    out["lincomb3"] = entry(ms, 4 * n * 8, cpu_timed(lambda: 0.75 * xs + 0.25 * ys + 0.25 * zs * 0.5), ns / n, "wxb_vec_lincomb3: 0.75 Q + 0.25 Q1 + 0.25 rhs dt")
+    # Krylov basis of restart 20 (22 rows): 1-sync Gram-Schmidt product and fused row update, solution update
+    m = 22
+    V = torch.empty(m, n, dtype=torch.float64, device=q_d.device)
+    for i in range(m):
+        V[i].copy_(q_d if i % 2 else r_d)
+        V[i].mul_(1.0 + 0.01 * i)
+    Vs = numpy.random.default_rng(9).standard_normal((m, ns // 4))
+    ms = timed(lambda: ops.multidot(V, m, V[m - 2 :], 2))
+    out["multidot_22x2"] = entry(ms, m * n * 8, cpu_timed(lambda: Vs @ Vs[m - 2 :].T), Vs.shape[1] / n,
+                                 "wxb_vec_multidot: Q[:22] @ Q[20:22].T (fgmres.py:38) incl. the 44-value read-back")
+    c = numpy.linspace(0.1, 0.2, m - 2)
+
+    def gs_cpu():
+        a = Vs[m - 2] - Vs[: m - 2].T @ c
+        b = Vs[m - 1] - Vs[: m - 2].T @ c
+        a /= 1.7
+        return (b - a * 0.3) / 1.7
+
+    ms = timed(lambda: ops.gs1sync(V, m - 2, c, c, 1.0, 0.0, V[m - 2], V[m - 1]))
+    out["gs1sync_20"] = entry(ms, (m + 2) * n * 8, cpu_timed(gs_cpu), Vs.shape[1] / n, "wxb_vec_gs1sync: rows 20 and 21 against rows 0..19 (fgmres.py:60-69)")
+    ms = timed(lambda: ops.combine(c, V, 1.0, q_d, 1.0, out=tmp))
+    out["combine_20"] = entry(ms, (m - 2 + 2) * n * 8, cpu_timed(lambda: Vs[m - 1] + c @ Vs[: m - 2]), Vs.shape[1] / n, "wxb_vec_combine: x + Z[:20].T y (fgmres.py:246-249)")
+    out["launches"] = ops.launches + filt.launches
+    return out
 
 
 def run_shallow_water(args):
@@ -557,6 +639,7 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-sw", action="store_true", help="skip the shallow-water side measurement (configs[1])")
     ap.add_argument("--sw-nh", type=int, default=720, help="shallow-water elements per panel side")
+    ap.add_argument("--skip-stepops", action="store_true", help="skip the side measurement of the per-step kernels (filter, stage algebra, Krylov)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -11,7 +11,7 @@ Everything is produced by the UNMODIFIED reference run here (harness.py):
   dense system and ``kiops`` (wx_factory/solvers/kiops.py:10-346) on a seeded matrix with three phi-vectors:
   inputs, solutions, iteration counts, residual history / stats;
 * ``tests/golden/steps_<integrator>_<case>.npz``  final state after N steps of the reference's own ``Ros2`` +
-  fgmres, ``Epi(2)`` + kiops and ``Epi(3)`` + kiops around its own RHS on 6 thread-ranks (the drift report of
+  fgmres, ``Epi(2)`` + kiops, ``Epi(3)`` + kiops and ``Epi(3)`` + pmex (config/case6.ini) around its own RHS on 6 thread-ranks (the drift report of
   SURVEY.md section 8d), with the per-step solver iteration counts.
 """
 
@@ -43,6 +43,8 @@ STEP_CASES = {
     # jacobian_method = fd: the finite-difference JVP of the north star (the schema default is the complex step)
     "epi2_dcmip31": ("epi2", "dcmip31", 3, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
     "epi3_dcmip21": ("epi3", "dcmip21", 4, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
+    # config/case6.ini as shipped: Epi(3) + PMEX on the shallow-water Rossby-Haurwitz wave (BASELINE configs[0])
+    "epi3_case6": ("epi3", "case6", 4, 1.0, {"tolerance": 1e-7, "exponential_solver": "pmex", "jacobian_method": "fd"}),
 }
 
 
@@ -68,6 +70,7 @@ def make_solvers():
         from mpi4py import MPI
         from solvers.fgmres import fgmres
         from solvers.kiops import kiops
+        from solvers.pmex import pmex
 
         dev = CpuDevice(comm=MPI.COMM_WORLD)
         rng = numpy.random.default_rng(20261105)
@@ -89,6 +92,9 @@ def make_solvers():
             w, stats = kiops(taus, lambda v: J @ v, u, tol=1e-9, device=dev, **kw)
             out[f"ki_w_{tag}"] = w
             out[f"ki_stats_{tag}"] = numpy.array([float(s) for s in stats])
+            w, stats = pmex(taus, lambda v: J @ v, u, tol=1e-9, device=dev, **kw)
+            out[f"pm_w_{tag}"] = w
+            out[f"pm_stats_{tag}"] = numpy.array([float(s) for s in stats])
         return out
 
     out = harness.run_ranks(1, work)[0]
@@ -131,7 +137,8 @@ def make_integrators():
         QN = numpy.stack([q for q, _ in res])
         path = os.path.join(GOLDEN, f"steps_{name}.npz")
         numpy.savez_compressed(path, QN=QN, nsteps=numpy.int64(nsteps), dt=numpy.float64(dt), iterations=numpy.array(res[0][1]),
-                               tolerance=numpy.float64(extra["tolerance"]), gmres_restart=numpy.int64(extra.get("gmres_restart", 0)))
+                               tolerance=numpy.float64(extra["tolerance"]), gmres_restart=numpy.int64(extra.get("gmres_restart", 0)),
+                               exponential_solver=numpy.str_(extra.get("exponential_solver", "")))
         Q0 = numpy.stack([s.Q for s in st])
         print(f"{name}: {nsteps} steps of dt={dt}, iterations {res[0][1]}, |QN-Q0|/|Q0| = {numpy.linalg.norm(QN-Q0)/numpy.linalg.norm(Q0):.3e}, "
               f"{os.path.getsize(path)/1e6:.2f} MB")

@@ -1,7 +1,7 @@
 # timing experiments: WXB_KERNEL_OPTS bit mask (1 skip faces, 2 skip nodes [wrong results], 4 no TMA staging, 8 L2 prefetch)
 for d in ${@:-0 4 12}; do
 echo "== WXB_KERNEL_OPTS=$d"
-WXB_KERNEL_OPTS=$d timeout 600 python bench.py --steps 20 --warmup 3 --skip-cpu --skip-sw --e2e-steps 3 2>&1 | tail -1 | python -c "
+WXB_KERNEL_OPTS=$d timeout 600 python bench.py --steps 20 --warmup 3 --skip-cpu --skip-sw --skip-stepops --e2e-steps 3 2>&1 | tail -1 | python -c "
 import json,sys
 d=json.loads(sys.stdin.read())
 for k in ('roofline','roofline_jvp'):

@@ -17,7 +17,8 @@ FILTER_TOL = 1e-14
 
 
 def rel(a, b):
-    return numpy.linalg.norm(a - b) / numpy.linalg.norm(b)
+    nb = numpy.linalg.norm(b)
+    return numpy.linalg.norm(a - b) / (nb if nb > 0 else 1.0)  # rho*w is identically zero in the initial states
 
 
 @pytest.mark.parametrize("name", ["dcmip21", "dcmip21_n5", "dcmip31_n4"])

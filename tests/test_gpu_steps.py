@@ -23,7 +23,7 @@ def _rel(a, b):
     return numpy.linalg.norm(a - b) / numpy.linalg.norm(b)
 
 
-@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3")])
+@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi3_case6", "case6", "epi3")])
 def test_steps_follow_reference(golden, name, case, kind):
     import torch
 
@@ -32,7 +32,7 @@ def test_steps_follow_reference(golden, name, case, kind):
     g = numpy.load(os.path.join(GOLDEN, f"steps_{name}.npz"))
     prob, ex = golden(case)
     rhs = RhsB200(prob)
-    param = types.SimpleNamespace(tolerance=float(g["tolerance"]), gmres_restart=int(g["gmres_restart"]) or 20, exponential_solver="kiops",
+    param = types.SimpleNamespace(tolerance=float(g["tolerance"]), gmres_restart=int(g["gmres_restart"]) or 20, exponential_solver=str(g["exponential_solver"]) if "exponential_solver" in g.files else "kiops",
                                   linear_solver="fgmres", verbose_solver=0)
     integ = integrators.Ros2(param, rhs.full) if kind == "ros2" else integrators.Epi(param, int(kind[3]), rhs.full)
     Q = torch.from_numpy(ex["Q0"]).cuda()
@@ -47,7 +47,9 @@ def test_steps_follow_reference(golden, name, case, kind):
     print(f"drift {name}: {drift:.3e} after {int(g['nsteps'])} steps, iterations {its} (reference {g['iterations'].tolist()}), "
           f"vector kernels launched {integ.ops.launches}")
     assert its == [int(i) for i in g["iterations"]]
-    assert drift <= STEP_TOL
+    # epi3_case6 (PMEX at dt = 1800 s) amplifies a 2e-16 input perturbation to 1.4e-8 (tests/test_integrators_host.py):
+    # its bound is the solver tolerance
+    assert drift <= (1e-7 if name == "epi3_case6" else STEP_TOL)
     rhs.close()
 
 

@@ -38,12 +38,12 @@ def test_tvdrk3_bit_identical_to_reference_trajectory():
     assert numpy.array_equal(Q.numpy(), g["QN"])  # the oracle is bit-identical to the reference, the stage algebra too
 
 
-@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3")])
+@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi3_case6", "case6", "epi3")])
 def test_implicit_and_exponential_steps_follow_reference(name, case, kind):
     path = os.path.join(GOLDEN, f"steps_{name}.npz")
     g = numpy.load(path)
     rhs, Q = _setup(case)
-    param = types.SimpleNamespace(tolerance=float(g["tolerance"]), gmres_restart=int(g["gmres_restart"]) or 20, exponential_solver="kiops",
+    param = types.SimpleNamespace(tolerance=float(g["tolerance"]), gmres_restart=int(g["gmres_restart"]) or 20, exponential_solver=str(g["exponential_solver"]) if "exponential_solver" in g.files else "kiops",
                                   linear_solver="fgmres", verbose_solver=0)
     ops = CpuVecOps()
     integ = integrators.Ros2(param, rhs, ops=ops) if kind == "ros2" else integrators.Epi(param, int(kind[3]), rhs, ops=ops)
@@ -57,4 +57,7 @@ def test_implicit_and_exponential_steps_follow_reference(name, case, kind):
     # the solvers stop at tolerance 1e-7; two implementations agree far below that because they follow the same
     # iterates: what differs is the rounding of the reductions, amplified by 1/eps ~ 2900 in the FD products and by the
     # incomplete orthogonalisation (measured here: ros2 2e-13, epi2 1.9e-10, epi3 1e-11)
-    assert _rel(Q.numpy(), g["QN"]) <= (1e-11 if kind == "ros2" else 1e-8)
+    # epi3_case6 (Epi(3) + PMEX at the config's full dt = 1800 s) is conditioned at the solver tolerance itself: changing
+    # the initial state by 2e-16 relative moves this result by 1.4e-8 (same code, same machine), so the bound there is the
+    # solver tolerance 1e-7 (measured 1.3e-8)
+    assert _rel(Q.numpy(), g["QN"]) <= (1e-11 if kind == "ros2" else 1e-7 if name == "epi3_case6" else 1e-8)

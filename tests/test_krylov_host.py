@@ -8,7 +8,7 @@ import numpy
 import torch
 
 from vecops_cpu import CpuVecOps
-from wxfactory_b200.krylov import fgmres, kiops
+from wxfactory_b200.krylov import fgmres, kiops, pmex
 
 G = numpy.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "krylov_small.npz"))
 
@@ -51,4 +51,16 @@ def test_kiops_reproduces_reference_substeps_and_result():
         assert [int(stats[i]) for i in (0, 1, 2, 3, 5)] == [int(want[i]) for i in (0, 1, 2, 3, 5)]
         assert abs(stats[4] - want[4]) <= 1e-3 * want[4]
         ref = G[f"ki_w_{tag}"]
+        assert numpy.linalg.norm(w.numpy() - ref) <= 1e-11 * numpy.linalg.norm(ref)
+
+
+def test_pmex_reproduces_reference_substeps_and_result():
+    J = G["ki_J"]
+    A = lambda v: _t(J @ v.numpy())  # noqa: E731
+    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True))):
+        w, stats = pmex(taus, A, _t(G["ki_u"]), tol=1e-9, ops=CpuVecOps(), **kw)
+        want = G[f"pm_stats_{tag}"]
+        assert [int(stats[i]) for i in (0, 1, 2, 3, 5, 6)] == [int(want[i]) for i in (0, 1, 2, 3, 5, 6)]
+        assert abs(stats[4] - want[4]) <= 1e-3 * want[4]
+        ref = G[f"pm_w_{tag}"]
         assert numpy.linalg.norm(w.numpy() - ref) <= 1e-11 * numpy.linalg.norm(ref)

@@ -69,27 +69,38 @@
 #define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
 #endif
 
-#ifndef WXB_TRACE_A
-#define WXB_TRACE_A 1  // trace fields (rho, u1, u2, w, rho theta, sound speed) and the log p lift folded into the
-                       // derivative matrix: no exp / reciprocal in the interface pass.  0: (rho, rho u, rho theta,
-                       // log rho theta) with the face pressure recomputed per face point
+// Formulation knobs of the trace / interface path (A/B'd on B200: profiles/r01_trace_variants.log):
+#ifndef WXB_TRACE_FIELDS
+#define WXB_TRACE_FIELDS 1  // 0: rho, rho u1, rho u2, rho w, rho theta, log(rho theta)  (face pressure = one exp per side and reader)
+                            // 1: rho, u1, u2, w, rho theta, a = sqrt(gamma p / rho)      (no exp / reciprocal in the interface pass)
+                            // 2: rho, rho u1, rho u2, rho w, rho theta, p                (no exp in the interface pass)
+#endif
+#ifndef WXB_FOLD_LOGP
+#define WXB_FOLD_LOGP 1     // derivative + lift of log p as one matrix on log(Rd/p0 rho theta) (see O_DLP); needed by fields 1, 2
+#endif
+#ifndef WXB_TRACE_MAP
+#define WXB_TRACE_MAP 0     // euler_traces: 0 = both sides of a line per thread (shares the line's loads), 1 = one (line, side)
+                            // per thread and round (all lanes busy, but 0.32 vs 0.22 ms: two dependent rounds on warp 0)
+#endif
+#ifndef WXB_TR_MINB
+#define WXB_TR_MINB 0       // resident blocks per SM euler_traces is compiled for (0: no register cap)
+#endif
+#if WXB_TRACE_FIELDS != 0 && !WXB_FOLD_LOGP
+#error "trace fields 1 and 2 carry no log(rho theta): they need WXB_FOLD_LOGP"
 #endif
 
 namespace {
 
 constexpr int NVAR = 5;
-// trace fields per face point.  WXB_TRACE_A: rho, u1, u2, w, rho*theta, a = sqrt(gamma p / rho) -- what the Rusanov
-// flux consumes, formed once per trace point here instead of once per side and per reader in euler_main.
-// Otherwise: the 5 variables + log(rho*theta) as extrapolated (before the exp).
-constexpr int NTR = 6;
-constexpr int NFF = WXB_TRACE_A ? 6 : 7;  // interface results per face point kept for the lift
+constexpr int NTR = 6;                      // trace fields per face point (WXB_TRACE_FIELDS)
+constexpr int NFF = WXB_FOLD_LOGP ? 6 : 7;  // interface results per face point kept for the lift
 
 // extrapolated line sums -> the trace fields (l0 = log rho, l4 = log(rho theta), m1..m3 = momenta)
 __device__ __forceinline__ void trace_fields(double m1, double m2, double m3, double l0, double l4, double out[NTR]) {
     const double rho = exp(l0);
     out[0] = rho;
     out[4] = exp(l4);
-#if WXB_TRACE_A
+#if WXB_TRACE_FIELDS == 1
     const double r = 1.0 / rho;
     out[1] = m1 * r;
     out[2] = m2 * r;
@@ -101,7 +112,11 @@ __device__ __forceinline__ void trace_fields(double m1, double m2, double m3, do
     out[1] = m1;
     out[2] = m2;
     out[3] = m3;
+#if WXB_TRACE_FIELDS == 2
+    out[5] = WXB_P0 * exp(WXB_GAMMA * (l4 + WXB_LOG_RD_P0));  // pde_euler_cubesphere.py:158-160 from the extrapolated log
+#else
     out[5] = l4;
+#endif
 #endif
 }
 
@@ -187,7 +202,13 @@ __device__ __forceinline__ void line_of(int d, int pt, int& base, int& step) {
 // ------------------------------------------------------------------------------------------------------
 // traces: every element's 6 faces x 6 fields -> a.trace (read by the neighbours in euler_main, packed for other ranks)
 template <int N>
-__global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a) {
+__global__ void
+#if WXB_TR_MINB
+__launch_bounds__(Cfg<N>::THREADS, WXB_TR_MINB)
+#else
+__launch_bounds__(Cfg<N>::THREADS)
+#endif
+euler_traces(const EvalArgs a) {
     using C = Cfg<N>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
     __shared__ double s_ext[2 * N];
@@ -220,7 +241,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) euler_traces(const EvalArgs a
     }
     __syncthreads();
     if (!active) return;
-#if WXB_TRACE_A
+#if WXB_TRACE_MAP
     // 6F trace points per element, one (line, side) per thread and round: all lanes of a warp carry a point (with both
     // sides per thread the 3F lines fill only 3/4 of the block's lanes, and the per-point exp/reciprocal work dominates)
     for (int tp = node; tp < 6 * F; tp += P) {
@@ -287,7 +308,7 @@ __device__ __forceinline__ void make_info(const EvalArgs& a, int e, int F, int P
 //   own / nb : the 6 trace fields of this element's side and of the facing side (already flipped / rotated)
 //   out[0..3] = F* rows rho, rho u1, rho u2, rho theta ; out[4] = wflux_adv* ; out[5] = wflux_pres* (own side) ;
 //   out[6] = log(p_itf own side)                 (fluxes.py:150-222,326-403,507-582; rhs_dfr.py:106-139)
-#if WXB_TRACE_A
+#if WXB_TRACE_FIELDS == 1
 // traces carry (rho, u1, u2, w, rho theta, a): momenta and pressure are products, the signal speed needs one sqrt of
 // the metric term; out[0..5] only (the own-side log p of the lift is folded into the derivative matrix, see O_DLP)
 template <int N>
@@ -324,7 +345,7 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
 #else
 template <int N>
 __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
-                                              const double own[NTR], const double nb[NTR], const double fm[4], double out7[7]) {
+                                              const double own[NTR], const double nb[NTR], const double fm[4], double out7[NFF]) {
     // interface metric, single-valued per physical face
     const double sg = fm[0], hd0 = fm[1], hd1 = fm[2], hd2 = fm[3];
     const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
@@ -348,12 +369,14 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     if (bc) {  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
         if (side == 0) uL = -uR; else uR = -uL;
     }
+#if WXB_TRACE_FIELDS == 2
+    const double pL = L[5], pR = R[5];  // the face pressure comes with the trace
+#else
     // face pressure p0*exp(gamma*log(Rd/p0 * rho_theta)) (pde_euler_cubesphere.py:158-160) with
     // log(rho_theta) taken from the trace (field 5) instead of log(exp(.)): same value to rounding
-    const double lpL = WXB_LOG_P0 + WXB_GAMMA * (L[5] + WXB_LOG_RD_P0);
-    const double lpR = WXB_LOG_P0 + WXB_GAMMA * (R[5] + WXB_LOG_RD_P0);
     const double pL = WXB_P0 * exp(WXB_GAMMA * (L[5] + WXB_LOG_RD_P0));
     const double pR = WXB_P0 * exp(WXB_GAMMA * (R[5] + WXB_LOG_RD_P0));
+#endif
 #if WXB_RCP
     const double eigL = fabs(uL) + sqrt(hdd * WXB_GAMMA * pL * rL);
     const double eigR = fabs(uR) + sqrt(hdd * WXB_GAMMA * pR * rR);
@@ -370,7 +393,11 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     out7[4] = 0.5 * (sguL * L[3] + sguR * R[3] - es * (R[3] - L[3]));
     const double pown = side ? pL : pR;
     out7[5] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
+#if !WXB_FOLD_LOGP
+    const double lpL = WXB_LOG_P0 + WXB_GAMMA * (L[5] + WXB_LOG_RD_P0);
+    const double lpR = WXB_LOG_P0 + WXB_GAMMA * (R[5] + WXB_LOG_RD_P0);
     out7[6] = side ? lpL : lpR;  // log(p_itf) of the own side (rhs_dfr.py:113)
+#endif
 }
 
 #endif
@@ -725,7 +752,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             fl[(d * 6 + 4) * RS] = sgu * q[3];
             fl[(d * 6 + 5) * RS] = sg * hd2;
         }
-#if WXB_TRACE_A
+#if WXB_FOLD_LOGP
         col[MC::RLOGP * RS] = lg;  // log p = log p0 + gamma*lg (pde_euler_cubesphere.py:124); see O_DLP
 #else
         col[MC::RLOGP * RS] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
@@ -770,7 +797,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const double dm = s_op[C::O_DIFF + idx * N + m];
 #pragma unroll
             for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * RS + m * step];
-            dv[6] += (WXB_TRACE_A ? s_op[C::O_DLP + idx * N + m] : dm) * slp[m * step];
+            dv[6] += (WXB_FOLD_LOGP ? s_op[C::O_DLP + idx * N + m] : dm) * slp[m * step];
             if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[RS + m * step];
         }
         const double cw = s_op[C::O_CORR + idx * 2], ce = s_op[C::O_CORR + idx * 2 + 1];
@@ -778,7 +805,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
 #pragma unroll
         for (int v = 0; v < NFF; ++v) dv[v] += cw * *ffp(2 * d * NFF + v, pt) + ce * *ffp((2 * d + 1) * NFF + v, pt);
         // d(log p) + lift of the own-side face log p = gamma * (D + c_w (x) ext_w + c_e (x) ext_e) lg + const(idx)
-        if (WXB_TRACE_A) dv[6] = WXB_GAMMA * dv[6] + s_op[C::O_KLP + idx];
+        if (WXB_FOLD_LOGP) dv[6] = WXB_GAMMA * dv[6] + s_op[C::O_KLP + idx];
 #pragma unroll
         for (int v = 0; v < 4; ++v) acc[v] += dv[v];
         const double wpres = col[(MC::RFL + d * 6 + 5) * RS];

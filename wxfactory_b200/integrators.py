@@ -14,7 +14,7 @@ import math
 from collections import deque
 from time import time
 
-from .krylov import fgmres, kiops
+from .krylov import fgmres, kiops, pmex
 from .rhs import MatvecOpFd, MatvecOpRat, RhsB200
 from .stepops import VecOps
 
@@ -134,16 +134,16 @@ _EPI_COEFS = {  # epi.py:44-61
 
 
 class Epi(Integrator):
-    """Multistep exponential propagation iterative integrators of order 2..6 with KIOPS (epi.py:30-363)."""
+    """Multistep exponential propagation iterative integrators of order 2..6 with KIOPS or PMEX (epi.py:30-363)."""
 
     def __init__(self, param, order, rhs, init_method=None, init_substeps=1, **kwargs):
         super().__init__(param, rhs, **kwargs)
         self.rhs = rhs
         self.tol = param.tolerance
         self.krylov_size = 1
-        solver = getattr(param, "exponential_solver", "kiops")
-        if solver != "kiops":
-            raise ValueError(f"Unrecognized exponential solver {solver} (the B200 path provides kiops)")
+        self.exponential_solver = getattr(param, "exponential_solver", "kiops")
+        if self.exponential_solver not in ("kiops", "pmex"):
+            raise ValueError(f"Unrecognized exponential solver {self.exponential_solver} (the B200 path provides kiops and pmex)")
         if order not in _EPI_COEFS:
             raise ValueError(f"Unsupported order {order} for EPI method")
         self.A = _EPI_COEFS[order]
@@ -185,8 +185,11 @@ class Epi(Integrator):
                 r = o.combine((-1.0, -1.0), _rows(o, rhs.reshape(-1), unit(dq)), 1.0, self.previous_rhs[i].reshape(-1))
                 for k, row in enumerate(self.A, start=2):
                     o.combine((row[i],), r.view(1, -1), 1.0, vec[k], 1.0, out=vec[k])
-        phiv, stats = kiops([1.0], matvec, vec, tol=self.tol, m_init=self.krylov_size, mmin=16, mmax=64, task1=False, ops=o)
-        self.krylov_size = math.floor(0.7 * stats[5] + 0.3 * self.krylov_size)
+        if self.exponential_solver == "pmex":  # epi.py:314-315: default m_init / mmin, no Krylov-size memory
+            phiv, stats = pmex([1.0], matvec, vec, tol=self.tol, mmax=64, task1=False, ops=o)
+        else:  # epi.py:325-338
+            phiv, stats = kiops([1.0], matvec, vec, tol=self.tol, m_init=self.krylov_size, mmin=16, mmax=64, task1=False, ops=o)
+            self.krylov_size = math.floor(0.7 * stats[5] + 0.3 * self.krylov_size)
         self.kiops_stats = stats
         self.solver_info = SolverInfo(total_num_it=stats[2])
         if self.n_prev > 0:

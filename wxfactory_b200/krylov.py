@@ -1,7 +1,7 @@
 """Device-resident Krylov solvers for the callers of the RHS / JVP.
 
-``fgmres`` and ``kiops`` keep the reference's signatures, return values and scalar control flow
-(wx_factory/solvers/fgmres.py:98-281, wx_factory/solvers/kiops.py:10-346) so that ``Ros2`` and ``Epi`` can call
+``fgmres``, ``kiops`` and ``pmex`` keep the reference's signatures, return values and scalar control flow
+(wx_factory/solvers/fgmres.py:98-281, wx_factory/solvers/kiops.py:10-346, wx_factory/solvers/pmex.py:8-374) so that ``Ros2`` and ``Epi`` can call
 them unchanged; what differs is where the work happens: the Krylov bases live on the GPU and every full-length
 operation is one launch of csrc/stepops.cu through ``VecOps`` (multi-dot with a fixed-order reduction, fused
 Gram-Schmidt row updates, linear combinations).  Only the small projected matrices (R, T, K, H, Givens rotations,
@@ -18,7 +18,7 @@ from time import time
 import numpy
 import scipy.linalg
 
-__all__ = ["fgmres", "kiops"]
+__all__ = ["fgmres", "kiops", "pmex"]
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -305,3 +305,163 @@ def kiops(tau_out, A, u, tol=1e-7, m_init=10, mmin=10, mmax=128, iop=2, task1=Fa
         for k in range(nsteps):
             ops.scale(w[k], 1.0 / tau_out[k])
     return w, (step, reject, krystep, exps, conv, m)
+
+
+# ------------------------------------------------------------------------------------------------------
+# PMEX: KIOPS with a low-synchronisation (2-step Gauss-Seidel) orthogonalisation and a norm estimate
+# ------------------------------------------------------------------------------------------------------
+def pmex(tau_out, A, u, tol=1e-7, delta=1.2, m_init=10, mmin=10, mmax=128, reuse_info=True, task1=False, device=None, ops=None):
+    """pmex.py:8-374: same phi-function problem and sub-stepping as ``kiops``; every Krylov step needs ONE reduction
+    (V[:j+1] @ V[j-1:j+1].T, pmex.py:168-176) from which the projection coefficients and, when it is safe, the norm of
+    the new vector (in extended precision, pmex.py:198-221) follow.  Returns (w, stats) with the reference's 7 stats:
+    (substeps, rejected, Krylov steps, matrix exponentials, error estimate, last Krylov size, norms that needed their
+    own reduction)."""
+    if ops is None:
+        raise ValueError("pmex needs a vector backend (stepops.VecOps)")
+    tau_out = numpy.atleast_1d(numpy.asarray(tau_out, dtype=float))
+    ppo, n = int(u.shape[0]), int(u.shape[1])
+    p = ppo - 1
+    if p == 0:
+        p = 1
+        u2 = ops.zeros(2, n)
+        u2[0].copy_(u[0])
+        u = u2
+    step = krystep = ireject = reject = exps = reg_comm_nrm = 0
+    sgn = float(numpy.sign(tau_out[-1]))
+    tau_now, tau_end = 0.0, float(abs(tau_out[-1]))
+    happy = False
+    j = 0
+    conv = 0.0
+    nsteps = len(tau_out)
+    m = max(mmin, min(m_init, mmax))
+    Vn = ops.zeros(mmax + 1, n)
+    Va = numpy.zeros((mmax + 1, p))
+    H = numpy.zeros((mmax + 1, mmax + 1))
+    Minv, M, N = numpy.eye(mmax), numpy.eye(mmax), numpy.zeros((mmax, mmax))
+    w = ops.zeros(nsteps, n)
+    w[0].copy_(u[0])
+    normU = float(numpy.max(ops.asum_rows(u[1:]))) if u.shape[0] > 1 else 0.0
+    if ppo > 1 and normU > 0:
+        ex = math.ceil(math.log2(normU))
+        nu, mu = 2.0 ** (-ex), 2.0**ex
+    else:
+        nu = mu = 1.0
+    u_flip = ops.zeros(p, n)
+    for k in range(p):
+        ops.combine((), None, 1.0, u[p - k], nu, out=u_flip[k])
+    tau = tau_end
+    gamma, gamma_mmax = (0.2, 0.1) if tau_end > 1 else (0.9, 0.6)
+    old_m, old_tau, ohm = -1, math.nan, math.nan
+    kestold = True
+    kest = 2.0
+    l = 0
+    beta = nrm = 0.0
+    numpy.seterr(divide="ignore", invalid="ignore")
+    while tau_now < tau_end:
+        if j == 0:
+            H[:, :] = 0.0
+            Vn[0].copy_(w[l])
+            for k in range(p - 1):
+                i = p - k + 1
+                Va[0, k] = (tau_now**i) / math.factorial(i) * mu
+            Va[0, p - 1] = mu
+            beta = math.sqrt(ops.dot(Vn[0], Vn[0]) + Va[0] @ Va[0])
+            ops.scale(Vn[0], 1.0 / beta)
+            Va[0] /= beta
+        while j < m:
+            j += 1
+            t = A(Vn[j - 1])
+            ops.combine(Va[j - 1], u_flip, 1.0, t, 1.0, out=Vn[j])
+            Va[j, : p - 1] = Va[j - 1, 1:p]
+            Va[j, p - 1] = 0.0
+            # the one reduction of the step (pmex.py:168-176)
+            g = ops.multidot(Vn, j + 1, Vn[j - 1 : j + 1], 2) + Va[: j + 1] @ Va[j - 1 : j + 1].T
+            if j > 1:
+                M[j - 1, : j - 1] = g[: j - 1, 0]
+                N[: j - 1, j - 1] = -g[: j - 1, 0]
+                Minv[j - 1, : j - 1] = -g[: j - 1, 0].T @ Minv[: j - 1, : j - 1]
+            rhs = (numpy.eye(j) + N[:j, :j] @ Minv[:j, :j]) @ g[:j, 1]
+            # same call as the reference (pmex.py:190-192), including its default `lower=False`
+            sol = scipy.linalg.solve_triangular(M[:j, :j], rhs, unit_diagonal=True, check_finite=False)
+            ops.combine(-sol, Vn[:j], 1.0, Vn[j], 1.0, out=Vn[j])
+            Va[j] -= sol @ Va[:j]
+            sum_sqrd = numpy.sum(numpy.array(g[:j, 1], numpy.longdouble) ** 2)  # extended precision (pmex.py:198-200)
+            if g[-1, 1] < sum_sqrd:
+                curr_nrm = math.sqrt(ops.dot(Vn[j], Vn[j]) + Va[j] @ Va[j])
+                reg_comm_nrm += 1
+            else:
+                curr_nrm = float(numpy.sqrt(g[-1, 1] - sum_sqrd))
+            if curr_nrm < tol:
+                happy = True
+                break
+            ops.scale(Vn[j], 1.0 / curr_nrm)
+            Va[j] /= curr_nrm
+            H[j, j - 1] = curr_nrm
+            H[:j, j - 1] = sol
+            krystep += 1
+        H[0, j] = 1.0
+        nrm = float(H[j, j - 1])
+        H[j, j - 1] = 0.0
+        F_half = scipy.linalg.expm(sgn * 0.5 * tau * H[: j + 1, : j + 1])
+        F = F_half @ F_half
+        exps += 1
+        H[j, j - 1] = nrm
+        if happy:
+            ohm, err = 0.0, 0.0
+            tau_new = min(tau_end - (tau_now + tau), tau)
+            m_new = m
+            happy = False
+        else:
+            err_half = abs(beta * nrm * F_half[j - 1, j])
+            err = abs(beta * nrm * F[j - 1, j])
+            old_ohm = ohm
+            ohm = numpy.float64(tau_end * err / (tau * tol))
+            order = float(numpy.log(numpy.float64(err) / err_half) / math.log(2))
+            if m != old_m and tau == old_tau and ireject >= 1:
+                kest = max(1.1, (ohm / old_ohm) ** (1 / (old_m - m)))
+                kestold = False
+            elif kestold or ireject == 0:
+                kest = 2
+                kestold = True
+            else:
+                kestold = True
+            remaining = tau_end - tau_now if ohm > delta else tau_end - (tau_now + tau)
+            same_tau = min(remaining, tau)
+            tau_opt = tau * (gamma / ohm) ** (1 / order)
+            tau_opt = min(remaining, max(tau / 5, min(5 * tau, tau_opt)))
+            m_opt = numpy.ceil(j + numpy.log(ohm / gamma) / numpy.log(kest))
+            m_opt = max(mmin, min(mmax, max(math.floor(3 / 4 * m), min(m_opt, math.ceil(4 / 3 * m)))))
+            if j == mmax:
+                if ohm > delta:
+                    m_new = j
+                    tau_new = tau * (gamma_mmax / ohm) ** (1 / order)
+                    tau_new = min(tau_end - tau_now, max(tau / 5, tau_new))
+                else:
+                    tau_new, m_new = tau_opt, m
+            else:
+                m_new = m if same_tau < tau else m_opt  # tau was cut to land on the end: keep m (pmex.py:301-305)
+                tau_new = same_tau
+        if ohm <= delta:
+            reject += ireject
+            step += 1
+            blown = sum(1 for k in range(l, nsteps) if abs(tau_out[k]) < abs(tau_now + tau))
+            if blown:
+                w[l + blown].copy_(w[l])
+                for k in range(blown):
+                    F2 = scipy.linalg.expm(sgn * (tau_out[l + k] - tau_now) * H[:j, :j])
+                    ops.combine(beta * F2[:j, 0], Vn[:j], out=w[l + k])
+                l += blown
+            ops.combine(beta * F[:j, 0], Vn[:j], out=w[l])
+            tau_now += tau
+            j = 0
+            ireject = 0
+            conv += err
+        else:
+            ireject += 1
+            H[0, j] = 0.0
+        old_tau, tau = tau, tau_new
+        old_m, m = m, int(m_new)
+    if task1:
+        for k in range(nsteps):
+            ops.scale(w[k], 1.0 / tau_out[k])
+    return w, (step, reject, krystep, exps, conv, m, reg_comm_nrm)

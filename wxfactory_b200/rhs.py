@@ -54,7 +54,7 @@ class RhsB200:
         self.group = process_group
         euler = problem.equations == "euler"
         self.num_var = problem.num_var
-        # trace fields per face point: the Euler kernels carry log(rho*theta) as a 6th field (csrc/euler3d.cu)
+        # trace fields per face point: the Euler kernels carry 6 (csrc/euler3d.cu, WXB_TRACE_FIELDS)
         self.num_trace = 6 if euler else 3
         nz = problem.nz if euler else 1
         self.part = build_partition(
@@ -443,3 +443,11 @@ class RhsBundleB200:
         self.problem = problem_from_reference(ranks)
         self.full = RhsB200(self.problem, device=device)
         self.shape = self.problem.state_shape
+        # the per-step exponential filter of the same operators object, when the configuration applies one
+        # (DFROperators.expfilter_apply, wx_factory/geometry/operators.py:101-119)
+        self.filter = None
+        ops0 = getattr(ranks[0], "ops", None)
+        if eq == "euler" and getattr(ops0, "expfilter_apply", False):
+            from .stepops import ExpFilterB200
+
+            self.filter = ExpFilterB200(self.full, numpy.asarray(ops0.expfilter, dtype=float))

@@ -1,0 +1,120 @@
+"""State file bridge: read and write the reference's restart files directly from the
+partitioned state of a B200 run, so that runs can start from, and be compared with, reference runs at any rank count.
+
+File format (wx_factory/output/state.py:9-33): ``numpy.save`` of the GLOBAL state
+``(6, num_var, [nz,] nh, nh, P)`` (``ProcessTopology.gather_cube``, wx_factory/process_topology.py:444-470: panels
+stacked on the first axis), followed by one text line with the configuration schema version and the raw INI text.
+File name (wx_factory/output/output_manager.py:76-95): ``state_vector_<hash>.<step:08d>.npy`` with
+``hash = hash((dt, nh_total, nz, n)) & 0xFFFFFFFFFFFF``.
+
+A rank of a 1/2/4/8-way partition holds the rows of element columns its slabs cover (partition.py); ``gather_state``
+/ ``scatter_state`` move between that flat local layout and the global array (through torch.distributed when there is
+more than one rank; the file itself is written / read by rank 0 like the reference's ``SingleProcess`` block).
+"""
+
+import io
+import os
+
+import numpy
+
+from .layout import local_state, scatter_back
+
+STATE_VERSION = "0.1"  # config/config-format.json "version" of the reference this was written against
+
+
+def config_hash(dt, num_elements_horizontal_total, num_elements_vertical, num_solpts):
+    """output_manager.py:76-83 (Python's tuple hash of numbers is deterministic)."""
+    return (dt, num_elements_horizontal_total, num_elements_vertical, num_solpts).__hash__() & 0xFFFFFFFFFFFF
+
+
+def state_file_name(output_dir, step_id, dt, num_elements_horizontal_total, num_elements_vertical, num_solpts):
+    """output_manager.py:91-95."""
+    h = config_hash(dt, num_elements_horizontal_total, num_elements_vertical, num_solpts)
+    return f"{output_dir}/state_vector_{h:012x}.{step_id:08d}.npy"
+
+
+def save_state(state, config_content, output_file_name, state_version=STATE_VERSION):
+    """state.py:9-17: the array, then ``<version>\\n`` and the INI text."""
+    with open(output_file_name, "wb+") as f:
+        numpy.save(f, numpy.asarray(state))
+        f.write(bytes(f"{state_version}\n", "utf-8"))
+        f.write(bytes(config_content, "utf-8"))
+
+
+def load_state(input_file_name):
+    """state.py:20-33 without building a Configuration: returns (state, state_version, config_content)."""
+    with open(input_file_name, "rb") as f:
+        state = numpy.load(f)
+        version = str(f.readline(), "utf-8").strip()
+        content = "\n".join(str(line, "utf-8") for line in f.readlines()).strip()
+    return state, version, content
+
+
+def gather_state(rhs, local, group=None):
+    """Flat local state of every rank (numpy or CUDA tensor) -> global ``prob.state_shape`` numpy array on rank 0
+    (None elsewhere).  ``rhs``: this rank's ``RhsB200`` (knows the problem and the partition)."""
+    from .partition import build_partition
+
+    prob = rhs.prob
+    loc = local.detach().cpu().numpy() if hasattr(local, "detach") else numpy.asarray(local)
+    loc = loc.reshape(-1)
+    if rhs.nranks == 1:
+        return scatter_back(prob, rhs.part, loc, numpy.empty(prob.state_shape))
+    import torch
+    import torch.distributed as dist
+
+    pieces = [None] * rhs.nranks if rhs.rank == 0 else None
+    dist.gather_object(loc, pieces, dst=0, group=group)
+    if rhs.rank != 0:
+        return None
+    out = numpy.empty(prob.state_shape)
+    euler = prob.equations == "euler"
+    for r, piece in enumerate(pieces):
+        part = rhs.part if r == rhs.rank else build_partition(
+            prob.nh, prob.nz if euler else 1, prob.n, prob.bnd_sn, prob.bnd_we, nranks=rhs.nranks, rank=r,
+            num_var=rhs.num_trace, nfaces=6 if euler else 4, trace_layout="element" if euler else "field")
+        scatter_back(prob, part, piece, out)
+    del torch
+    return out
+
+
+def scatter_state(rhs, global_state, group=None):
+    """Global state on rank 0 (ignored elsewhere) -> this rank's flat local numpy state."""
+    if rhs.nranks == 1:
+        return rhs.local_state(global_state)
+    import torch.distributed as dist
+
+    box = [numpy.asarray(global_state) if rhs.rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    return rhs.local_state(box[0])
+
+
+def write_restart(rhs, local, config_content, output_dir, step_id, dt, group=None):
+    """What OutputManager.step does when save_state_freq hits (output_manager.py:136-143)."""
+    total = gather_state(rhs, local, group)
+    if rhs.rank != 0:
+        return None
+    prob = rhs.prob
+    os.makedirs(os.path.abspath(output_dir), exist_ok=True)
+    name = state_file_name(output_dir, step_id, dt, prob.nh, prob.nz if prob.equations == "euler" else 1, prob.n)
+    save_state(total, config_content, name)
+    return name
+
+
+def read_restart(rhs, input_file_name, group=None):
+    """OutputManager.load_state_from_file (output_manager.py:97-124): the local state of this rank + the INI text."""
+    state = content = None
+    if rhs.rank == 0:
+        state, _, content = load_state(input_file_name)
+        if tuple(state.shape) != tuple(rhs.prob.state_shape):
+            raise ValueError(f"ERROR reading state vector from file. The shape is wrong! ({state.shape}, should be {rhs.prob.state_shape})")
+    return scatter_state(rhs, state, group), content
+
+
+def dumps(state, config_content, state_version=STATE_VERSION):
+    """The file's bytes (for tests)."""
+    b = io.BytesIO()
+    numpy.save(b, numpy.asarray(state))
+    b.write(bytes(f"{state_version}\n", "utf-8"))
+    b.write(bytes(config_content, "utf-8"))
+    return b.getvalue()

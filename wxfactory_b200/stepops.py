@@ -139,9 +139,14 @@ class VecOps:
     def max_rel_change(self, update, x):
         """max |update / x| over x != 0 (stagnation test of fgmres.py:257-262, once per restart cycle)."""
         nz = x != 0
-        if not bool(nz.any()):
-            return math.inf
-        return float((update[nz] / x[nz]).abs().max())
+        loc = float((update[nz] / x[nz]).abs().max()) if bool(nz.any()) else -1.0  # -1: no non-zero entry on this rank
+        if self.world_size > 1:  # one answer on every rank (the reference takes the local maximum: ranks could part ways)
+            import torch.distributed as dist
+
+            t = self.torch.full((1,), loc, dtype=self.torch.float64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            loc = float(t.item())
+        return loc if loc >= 0.0 else math.inf
 
     def scale(self, x, s, out=None):
         return self.combine((), x, 1.0, x, s, out=x if out is None else out)
