@@ -67,10 +67,10 @@ def b_jvp(n):
 
 # DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
 # of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
-# profiles/r01_final_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
+# profiles/r01_final2_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
 NCU_TRAFFIC_NODES = 10616832
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.424807e9 + 0.708674e9 + 4.525539e9 + 0.430559e9) / NCU_TRAFFIC_NODES,
-                        "jvp": (0.849551e9 + 1.132855e9 + 4.988846e9 + 0.440028e9) / NCU_TRAFFIC_NODES}
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.424690e9 + 0.707571e9 + 4.520823e9 + 0.427751e9) / NCU_TRAFFIC_NODES,
+                        "jvp": (0.849378e9 + 1.132953e9 + 4.988523e9 + 0.441481e9) / NCU_TRAFFIC_NODES}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -382,7 +382,7 @@ def run_b200(args):
                 "unit": "GB/s",
                 "frac": ach / peak,
                 "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
-                "traffic_source": "profiles/r01_final_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
+                "traffic_source": "profiles/r01_final2_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
                 "kernels": ["euler_traces<4>", "euler_main<4>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bytes_per_node,
@@ -499,7 +499,8 @@ def measure_stepops(rhs, q_d, r_d, peak, reps=10):
                              "wxb_expfilter: ((sqrtG Q) @ expfilter_new) * inv_sqrtG as three 1-D passes")
     # SSP-RK3 stage combination: 3 reads + 1 write
     tmp = torch.empty_like(q_d)
-    ms = timed(lambda: ops.lincomb3(0.75, q_d, 0.25, r_d, 0.25, r_d, 0.5, out=tmp))
+    q1_d = q_d * 1.01  # a third, distinct input: the kernel reads 3 arrays and writes 1
+    ms = timed(lambda: ops.lincomb3(0.75, q_d, 0.25, q1_d, 0.25, r_d, 0.5, out=tmp))
     out["lincomb3"] = entry(ms, 4 * n * 8, cpu_timed(lambda: 0.75 * xs + 0.25 * ys + 0.25 * zs * 0.5), ns / n, "wxb_vec_lincomb3: 0.75 Q + 0.25 Q1 + 0.25 rhs dt")
     # Krylov basis of restart 20 (22 rows): 1-sync Gram-Schmidt product and fused row update, solution update
     m = 22

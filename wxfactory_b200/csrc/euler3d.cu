@@ -2,7 +2,8 @@
 //
 // Two kernels per evaluation instead of the reference's ~150 numpy expressions:
 //
-//   euler_traces  element -> 6 face traces of the 5 variables (rho and rho*theta in log space)
+//   euler_traces  element -> 6 face traces (rho and rho*theta extrapolated in log space), stored in the form the flux
+//                 consumes: rho, u1, u2, w, rho*theta, sound speed (WXB_TRACE_FIELDS)
 //                 = RHSDirecFluxReconstruction_mpi.solution_extrapolation (wx_factory/rhs/rhs_dfr.py:50-71)
 //   euler_main    everything else, one thread per solution point, element fields staged in shared memory:
 //                 pointwise fluxes          wx_factory/pde/pde_euler_cubesphere.py:72-124
@@ -81,6 +82,9 @@
 #ifndef WXB_TRACE_MAP
 #define WXB_TRACE_MAP 0     // euler_traces: 0 = both sides of a line per thread (shares the line's loads), 1 = one (line, side)
                             // per thread and round (all lanes busy, but 0.32 vs 0.22 ms: two dependent rounds on warp 0)
+#endif
+#ifndef WXB_SYM
+#define WXB_SYM 0           // fields 1: Rusanov flux written in (own, facing) form without sorting the states into L / R
 #endif
 #ifndef WXB_TR_MINB
 #define WXB_TR_MINB 0       // resident blocks per SM euler_traces is compiled for (0: no register cap)
@@ -316,6 +320,28 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
                                               const double own[NTR], const double nb[NTR], const double fm[4], double out[NFF]) {
     const double sg = fm[0], hd0 = fm[1], hd1 = fm[2], hd2 = fm[3];
     const double hdd = d == 0 ? hd0 : (d == 1 ? hd1 : hd2);
+#if WXB_SYM
+    // The Rusanov flux is symmetric in its two states up to the sign of the jump: with o = own side, f = facing side
+    // and sgn = +1 when the own side is L (max-side face), F* = (F(o) + F(f))/2 - sgn * eig sqrtG (q_f - q_o)/2.
+    // No L/R sorting of the 12 values.
+    const double uo = d == 0 ? own[1] : (d == 1 ? own[2] : own[3]);
+    double uf = d == 0 ? nb[1] : (d == 1 ? nb[2] : nb[3]);
+    if (bc) uf = -uo;  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
+    constexpr double inv_gamma = 1.0 / WXB_GAMMA;
+    const double po = own[5] * own[5] * (own[0] * inv_gamma), pf = nb[5] * nb[5] * (nb[0] * inv_gamma);  // a^2 rho / gamma
+    const double sh = sqrt(hdd);
+    const double eig = fmax(fabs(uo) + sh * own[5], fabs(uf) + sh * nb[5]);  // |u| + sqrt(h^dd gamma p / rho)
+    const double sguo = sg * uo, sguf = sg * uf, es = side ? eig * sg : -(eig * sg);
+    const double mo1 = own[0] * own[1], mo2 = own[0] * own[2], mo3 = own[0] * own[3];
+    const double mf1 = nb[0] * nb[1], mf2 = nb[0] * nb[2], mf3 = nb[0] * nb[3];
+    out[0] = 0.5 * (sguo * own[0] + sguf * nb[0] - es * (nb[0] - own[0]));
+    out[1] = 0.5 * ((sguo * mo1 + sg * hd0 * po) + (sguf * mf1 + sg * hd0 * pf) - es * (mf1 - mo1));
+    out[2] = 0.5 * ((sguo * mo2 + sg * hd1 * po) + (sguf * mf2 + sg * hd1 * pf) - es * (mf2 - mo2));
+    out[3] = 0.5 * (sguo * own[4] + sguf * nb[4] - es * (nb[4] - own[4]));
+    out[4] = 0.5 * (sguo * mo3 + sguf * mf3 - es * (mf3 - mo3));
+    out[5] = 0.5 * (sg * hd2 * po + sg * hd2 * pf) / po;
+}
+#else
     double L[NTR], R[NTR];
 #pragma unroll
     for (int v = 0; v < NTR; ++v) {
@@ -342,6 +368,7 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     const double pown = side ? pL : pR;
     out[5] = 0.5 * (sg * hd2 * pL + sg * hd2 * pR) / pown;
 }
+#endif
 #else
 template <int N>
 __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo& ei, int d, int side, int pt, bool bc,
@@ -515,7 +542,7 @@ struct MainCfg {
     // direct mode keeps only the 20 flux rows in shared memory (own traces are read back from a.trace)
     static constexpr int RFL = STAGED ? R_FL : 0, RLOGP = RFL + 18, RSGRHO = RFL + 19;
     static constexpr int ROWS = STAGED ? NROWS : NFLUX;
-    // interface results (6 faces x 7 values x F) reuse the dead rows when they fit
+    // interface results (6 faces x NFF values x F) reuse the dead rows when they fit
     static constexpr bool FF_ALIAS = STAGED && (NROWS - R_FF) * P >= 6 * NFF * F;
     static constexpr int FF_OWN = FF_ALIAS ? 1 : 6 * NFF * F;
     static constexpr int NBR = STAGED ? 6 * NTR : 1, NBE = STAGED ? Cfg<N>::EB : 1, NBF = STAGED ? F : 1;

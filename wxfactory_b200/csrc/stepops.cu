@@ -30,7 +30,7 @@ void set_err(wxb_handle* h, const char* fmt, ...) {  // same convention as wxb_a
 
 constexpr int VEC_THREADS = 256;
 constexpr int VEC_BLOCKS = 148 * 4;  // persistent grid-stride blocks: a multiple of the SM count
-constexpr int MD_ROWS = 8;           // basis rows per pass of the multi-dot kernel (register accumulators)
+constexpr int MD_ROWS = 12;          // basis rows per pass of the multi-dot kernel (register accumulators; restart 20 = 22 rows = 2 passes)
 
 // ------------------------------------------------------------------------------------------------------
 // exponential filter: one thread per node and variable pass; element fields staged in shared memory
@@ -61,6 +61,13 @@ __global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_ker
     }
     __syncthreads();
     const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
+    double fi[N], fj[N], fk[N];  // this node's three filter rows, read once (the passes are shared-memory bound)
+#pragma unroll
+    for (int m = 0; m < N; ++m) {
+        fi[m] = s_f[ii * N + m];
+        fj[m] = s_f[jj * N + m];
+        fk[m] = s_f[kk * N + m];
+    }
     // expfilter_new = (filter_x @ filter_y) @ filter_z with filter_d = kron(.., expfilter, ..).T: the passes commute
     // in exact arithmetic; x, y, z is the order of the reference's product (operators.py:115-119)
     if (active) {
@@ -68,7 +75,7 @@ __global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_ker
         for (int v = 0; v < NV; ++v) {
             double s = 0.0;
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(s_f[ii * N + m], s_a[le][v][node - ii + m], s);
+            for (int m = 0; m < N; ++m) s = fma(fi[m], s_a[le][v][node - ii + m], s);
             s_b[le][v][node] = s;
         }
     }
@@ -78,7 +85,7 @@ __global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_ker
         for (int v = 0; v < NV; ++v) {
             double s = 0.0;
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(s_f[jj * N + m], s_b[le][v][node + (m - jj) * N], s);
+            for (int m = 0; m < N; ++m) s = fma(fj[m], s_b[le][v][node + (m - jj) * N], s);
             s_a[le][v][node] = s;
         }
     }
@@ -89,7 +96,7 @@ __global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_ker
         for (int v = 0; v < NV; ++v) {
             double s = 0.0;
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(s_f[kk * N + m], s_a[le][v][node + (m - kk) * N * N], s);
+            for (int m = 0; m < N; ++m) s = fma(fk[m], s_a[le][v][node + (m - kk) * N * N], s);
             a.out[qo + v * vst] = s * inv;
         }
     }
@@ -194,6 +201,7 @@ __global__ void __launch_bounds__(VEC_THREADS) combine_kernel(long long n, int m
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
         double acc = 0.0;
+#pragma unroll 4
         for (int i = 0; i < m; ++i) acc = fma(cf.c[i], V[i * ldv + x], acc);
         if (y) acc = b0 * y[x] + acc;
         out[x] = acc * s;
@@ -207,6 +215,7 @@ __global__ void __launch_bounds__(VEC_THREADS) gs1sync_kernel(long long n, int m
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
         double a2 = 0.0, a1 = 0.0;
+#pragma unroll 4
         for (int i = 0; i < m; ++i) {
             const double v = Q[i * ldq + x];
             a2 = fma(v, s2.c[i], a2);
