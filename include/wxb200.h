@@ -24,6 +24,12 @@
  *                        wx_factory/device/device.py:201-214)
  *   wxb_destroy, wxb_last_error, wxb_version : lifetime / error convention (the reference raises Python
  *                        exceptions: wx_factory/rhs/rhs_selector.py:44,83)
+ *   wxb_set_expfilter / wxb_expfilter
+ *                     <- DFROperators.apply_filter_3d (wx_factory/geometry/operators.py:101-119,257-261)
+ *   wxb_vec_*         <- the full-state vector algebra of the callers: Tvdrk3 / Ros2 stage combinations
+ *                        (wx_factory/integrators/tvdrk3.py:13-17, ros2.py:30), the Gram-Schmidt products and updates of
+ *                        FGMRES, KIOPS and PMEX (wx_factory/solvers/fgmres.py:16-72, kiops.py:176-211, pmex.py:150-230),
+ *                        the NaN check (wx_factory/simulation/simulation.py:399-408); declared in the second half
  *
  * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative WXB_E*
  * code and never throws; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); work is

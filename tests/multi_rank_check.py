@@ -70,10 +70,46 @@ def main():
             print(f"{name}: {world} ranks vs 1 rank bit-identical={same}; vs reference {err:.2e} (bound {tol:.1e}) -> {'ok' if good else 'FAIL'}", flush=True)
         rhs.close()
         dist.barrier()
+    ok = steps_check(rank, world, local, dev) and ok
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, 0)
     dist.destroy_process_group()
     sys.exit(0 if int(flag.item()) else 1)
+
+
+def steps_check(rank, world, local, dev):
+    """The callers' side across ranks: Ros2 + FGMRES and Epi(2) + KIOPS with every Krylov vector split over the ranks
+    (dot products summed by NCCL all-reduce inside VecOps), the partitioned state gathered through the state-file bridge;
+    against the reference's trajectories (tests/golden/steps_*.npz)."""
+    import types
+
+    from wxfactory_b200 import integrators, state_io
+
+    ok = True
+    for name, case, kind in (("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2")):
+        prob, ex = load_problem(os.path.join(ROOT, "tests", "golden", case + ".npz"))
+        if (6 * prob.nh) % world:
+            continue
+        g = numpy.load(os.path.join(ROOT, "tests", "golden", f"steps_{name}.npz"))
+        rhs = RhsB200(prob, nranks=world, rank=rank, device=local)
+        param = types.SimpleNamespace(tolerance=float(g["tolerance"]), gmres_restart=int(g["gmres_restart"]) or 20,
+                                      exponential_solver="kiops", linear_solver="fgmres", verbose_solver=0)
+        integ = integrators.Ros2(param, rhs.full) if kind == "ros2" else integrators.Epi(param, int(kind[3]), rhs.full)
+        Q = torch.from_numpy(rhs.local_state(ex["Q0"])).to(dev)
+        its = []
+        for _ in range(int(g["nsteps"])):
+            integ.__prestep__(Q, float(g["dt"]))
+            Q = integ.__step__(Q, float(g["dt"]))
+            its.append(integ.solver_info.total_num_it)
+        total = state_io.gather_state(rhs, Q)
+        if rank == 0:
+            drift = numpy.linalg.norm(total - g["QN"].reshape(total.shape)) / numpy.linalg.norm(g["QN"])
+            good = its == [int(i) for i in g["iterations"]] and drift <= 1e-8
+            ok = ok and good
+            print(f"{name}: {world} ranks, iterations {its} (reference {g['iterations'].tolist()}), drift {drift:.2e} -> {'ok' if good else 'FAIL'}", flush=True)
+        rhs.close()
+        dist.barrier()
+    return ok
 
 
 if __name__ == "__main__":

@@ -48,7 +48,7 @@
 #define WXB_MINB3 4
 #endif
 #ifndef WXB_MINB4
-#define WXB_MINB4 10
+#define WXB_MINB4 7  // with the (rho, u, rho theta, a) traces: 7-8 blocks (122-142 registers, no spills) beat 10 (96, spills)
 #endif
 #ifndef WXB_MINB5
 #define WXB_MINB5 4
@@ -59,10 +59,6 @@
 #ifndef WXB_CH3
 #define WXB_CH3 0  // 1: Christoffel symbols loaded 9 at a time (fewer registers, less memory parallelism)
 #endif
-#ifndef WXB_MINB4
-#define WXB_MINB4 10
-#endif
-
 #ifndef WXB_FR_MIN_N
 #define WXB_FR_MIN_N 4  // lowest order that builds the per-face address table in euler_main
 #endif
@@ -84,7 +80,7 @@
                             // per thread and round (all lanes busy, but 0.32 vs 0.22 ms: two dependent rounds on warp 0)
 #endif
 #ifndef WXB_SYM
-#define WXB_SYM 0           // fields 1: Rusanov flux written in (own, facing) form without sorting the states into L / R
+#define WXB_SYM 1           // fields 1: Rusanov flux written in (own, facing) form without sorting the states into L / R
 #endif
 #ifndef WXB_TR_MINB
 #define WXB_TR_MINB 0       // resident blocks per SM euler_traces is compiled for (0: no register cap)

@@ -90,7 +90,7 @@ class VecOps:
                                       self._scratch.data_ptr(), _sp(self.torch, self.device)),
             "wxb_vec_multidot",
         )
-        self.launches += (m + 11) // 12 + 1  # MD_ROWS rows per pass + the final reduction (csrc/stepops.cu)
+        self.launches += (m + 7) // 8 + 1  # MD_ROWS rows per pass + the final reduction (csrc/stepops.cu)
         if self.world_size > 1:
             import torch.distributed as dist
 
