@@ -67,10 +67,10 @@ def b_jvp(n):
 
 # DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
 # of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
-# profiles/r01_final2_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
+# profiles/r01_final3_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
 NCU_TRAFFIC_NODES = 10616832
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.424690e9 + 0.707571e9 + 4.520823e9 + 0.427751e9) / NCU_TRAFFIC_NODES,
-                        "jvp": (0.849378e9 + 1.132953e9 + 4.988523e9 + 0.441481e9) / NCU_TRAFFIC_NODES}
+NCU_TRAFFIC_PER_NODE = {"rhs": (0.424689e9 + 0.706788e9 + 4.501844e9 + 0.420585e9) / NCU_TRAFFIC_NODES,
+                        "jvp": (0.849363e9 + 1.133382e9 + 4.966819e9 + 0.419694e9) / NCU_TRAFFIC_NODES}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -382,7 +382,7 @@ def run_b200(args):
                 "unit": "GB/s",
                 "frac": ach / peak,
                 "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
-                "traffic_source": "profiles/r01_final2_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
+                "traffic_source": "profiles/r01_final3_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
                 "kernels": ["euler_traces<4>", "euler_main<4>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bytes_per_node,

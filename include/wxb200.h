@@ -213,6 +213,11 @@ int64_t wxb_vec_multidot_scratch(int m, int k);
 int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
                      double* scratch_dev, void* stream);
 
+/* Scalar reductions (fixed order; scratch_dev as for wxb_vec_multidot(1, 1)):
+ *   kind 0: *out_dev = sum_i |x[i]|                  <- 1-norms of the phi vectors, kiops.py:111-116, pmex.py:91-98
+ *   kind 1: *out_dev = max_{x[i] != 0} |y[i] / x[i]|, -1 if x == 0   <- stagnation test update/x of fgmres.py:257-262 */
+int wxb_vec_reduce(int64_t n, int kind, const double* x, const double* y, double* out_dev, double* scratch_dev, void* stream);
+
 /* out = (b0 y + sum_{i<m} coef[i] V[i]) * s   <- V[j] - V[ilow:j].T @ H (kiops.py:199), V[j] / nrm (:208),
  * beta * F[:j,0] @ V[:j,:n] (:278,286), x + Z.T @ y of FGMRES (fgmres.py:246-249).  y may be NULL; out may alias y. */
 int wxb_vec_combine(int64_t n, int m, const double* coef_host, const double* V, int64_t ldv, double b0, const double* y, double s,

@@ -141,6 +141,23 @@ def test_gs1sync_matches_the_stand_in(ops, m):
     assert numpy.linalg.norm(got[m:] - want[m:]) <= 1e-14 * numpy.linalg.norm(want[m:]) * max(m, 1)
 
 
+def test_scalar_reductions(ops):
+    import torch
+
+    rng = numpy.random.default_rng(11)
+    U = rng.standard_normal((3, 200_003))
+    Ud = torch.from_numpy(U).cuda()
+    got = ops.asum_rows(Ud)
+    want = numpy.abs(U).sum(axis=1)
+    assert numpy.all(numpy.abs(got - want) <= 1e-13 * want)
+    x, u = U[0].copy(), U[1] * 1e-3
+    x[::7] = 0.0
+    got = ops.max_rel_change(torch.from_numpy(u).cuda(), torch.from_numpy(x).cuda())
+    nz = x != 0
+    assert got == float(numpy.max(numpy.abs(u[nz] / x[nz])))  # a maximum of correctly rounded quotients: exact
+    assert ops.max_rel_change(Ud[1], torch.zeros_like(Ud[0])) == float("inf")
+
+
 def test_vector_entry_points_reject_bad_arguments():
     from wxfactory_b200 import capi
 
@@ -149,3 +166,4 @@ def test_vector_entry_points_reject_bad_arguments():
     assert lib.wxb_vec_multidot(10, 65, None, 10, 1, None, 10, None, None, None) == -1
     assert lib.wxb_vec_multidot(10, 2, None, 10, 3, None, 10, None, None, None) == -1
     assert lib.wxb_vec_combine(10, 65, None, None, 10, 0.0, None, 1.0, None, None) == -1
+    assert lib.wxb_vec_reduce(10, 2, None, None, None, None, None) == -1

@@ -11,6 +11,7 @@
 //                       201-205), PMEX (wx_factory/solvers/pmex.py:150-230) and of the 1-sync FGMRES
 //                       (wx_factory/solvers/fgmres.py:38); fixed-order two-stage reduction (bit-reproducible run to run)
 //   wxb_vec_combine     out = (b0 y + sum_i c[i] V[i]) * s: kiops.py:199,208,278,286 / Krylov solution updates
+//   wxb_vec_reduce      sum |x| (kiops.py:111-116) and max |y/x| over x != 0 (fgmres.py:257-262)
 //   wxb_vec_gs1sync     the row updates of fgmres.py:60-69 (_ortho_1_sync_igs) in one pass over the basis
 //
 // The vector kernels are free functions of the C ABI (no handle): Krylov vectors are plain device arrays.
@@ -192,6 +193,41 @@ __global__ void multidot_final(int nblocks, int mk, const double* __restrict__ p
     out[t] = v;
 }
 
+// scalar reductions the solvers need once per call / restart cycle, two stages in a fixed order like the multi-dot:
+//   kind 0: sum |x|                       (1-norms of the phi-function vectors, kiops.py:111-116, pmex.py:91-98)
+//   kind 1: max |y / x| over x != 0, -1 when x has no non-zero entry   (stagnation test, fgmres.py:257-262)
+template <int KIND>
+__global__ void __launch_bounds__(VEC_THREADS) reduce_partial(long long n, const double* __restrict__ x, const double* __restrict__ y,
+                                                             double* __restrict__ partial) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    double acc = KIND == 0 ? 0.0 : -1.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += stride) {
+        if (KIND == 0) acc += fabs(x[i]);
+        else if (x[i] != 0.0) acc = fmax(acc, fabs(y[i] / x[i]));
+    }
+    __shared__ double s_red[VEC_THREADS / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double t = __shfl_down_sync(0xffffffffu, acc, o);
+        acc = KIND == 0 ? acc + t : fmax(acc, t);
+    }
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double v = s_red[0];
+        for (int w = 1; w < VEC_THREADS / 32; ++w) v = KIND == 0 ? v + s_red[w] : fmax(v, s_red[w]);
+        partial[blockIdx.x] = v;
+    }
+}
+
+template <int KIND>
+__global__ void reduce_final(int nblocks, const double* __restrict__ partial, double* __restrict__ out) {
+    if (blockIdx.x || threadIdx.x) return;
+    double v = partial[0];
+    for (int b = 1; b < nblocks; ++b) v = KIND == 0 ? v + partial[b] : fmax(v, partial[b]);
+    *out = v;
+}
+
 struct Coefs {
     double c[WXB_VEC_MAX_ROWS];
 };
@@ -320,6 +356,20 @@ int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, cons
             multidot_partial<2><<<blocks, VEC_THREADS, 0, s>>>(n, mm, V + row0 * ldv, ldv, W, ldw, scratch_dev, m, row0);
     }
     multidot_final<<<(m * k + 127) / 128, 128, 0, s>>>(blocks, m * k, scratch_dev, out_dev);
+    return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
+}
+
+int wxb_vec_reduce(int64_t n, int kind, const double* x, const double* y, double* out_dev, double* scratch_dev, void* stream) {
+    if (n <= 0 || (kind != 0 && kind != 1) || !x || (kind == 1 && !y) || !out_dev || !scratch_dev) return WXB_EINVAL;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int blocks = grid_for(n);
+    if (kind == 0) {
+        reduce_partial<0><<<blocks, VEC_THREADS, 0, s>>>(n, x, y, scratch_dev);
+        reduce_final<0><<<1, 32, 0, s>>>(blocks, scratch_dev, out_dev);
+    } else {
+        reduce_partial<1><<<blocks, VEC_THREADS, 0, s>>>(n, x, y, scratch_dev);
+        reduce_final<1><<<1, 32, 0, s>>>(blocks, scratch_dev, out_dev);
+    }
     return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
 }
 

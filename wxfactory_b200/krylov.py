@@ -21,6 +21,20 @@ import scipy.linalg
 __all__ = ["fgmres", "kiops", "pmex"]
 
 
+def _numpy_inf_nan(fn):
+    """Run fn with numpy's divide / invalid warnings off: the adaptivity formulas of KIOPS / PMEX rely on inf and nan
+    propagating like in the reference (e.g. log(0) when an error estimate vanishes) and must not change the caller's
+    error state."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        with numpy.errstate(divide="ignore", invalid="ignore"):
+            return fn(*args, **kwargs)
+
+    return wrapped
+
+
 # ------------------------------------------------------------------------------------------------------
 # FGMRES with the one-synchronisation Gram-Schmidt
 # ------------------------------------------------------------------------------------------------------
@@ -152,6 +166,7 @@ def fgmres(A, b, x0=None, tol=1e-5, restart=20, maxiter=None, preconditioner=Non
 # ------------------------------------------------------------------------------------------------------
 # KIOPS
 # ------------------------------------------------------------------------------------------------------
+@_numpy_inf_nan
 def kiops(tau_out, A, u, tol=1e-7, m_init=10, mmin=10, mmax=128, iop=2, task1=False, device=None, ops=None):
     """w[i] = phi_0(tau_i A) u[0] + phi_1(tau_i A) u[1] + ... (kiops.py:10-346), adaptive Krylov size and sub-step,
     incomplete orthogonalisation of length ``iop``.  ``u``: (p+1, n) device array.  Returns (w, stats) like the
@@ -204,7 +219,6 @@ def kiops(tau_out, A, u, tol=1e-7, m_init=10, mmin=10, mmax=128, iop=2, task1=Fa
         cnt = rows.stop - rows.start
         return ops.multidot(Vn[rows], cnt, Vn[jj].view(1, -1), 1)[:, 0] + Va[rows] @ Va[jj]
 
-    numpy.seterr(divide="ignore", invalid="ignore")
     while tau_now < tau_end:
         if j == 0:  # starting vector of this sub-step (kiops.py:151-168)
             Vn[0].copy_(w[l])
@@ -310,6 +324,7 @@ def kiops(tau_out, A, u, tol=1e-7, m_init=10, mmin=10, mmax=128, iop=2, task1=Fa
 # ------------------------------------------------------------------------------------------------------
 # PMEX: KIOPS with a low-synchronisation (2-step Gauss-Seidel) orthogonalisation and a norm estimate
 # ------------------------------------------------------------------------------------------------------
+@_numpy_inf_nan
 def pmex(tau_out, A, u, tol=1e-7, delta=1.2, m_init=10, mmin=10, mmax=128, reuse_info=True, task1=False, device=None, ops=None):
     """pmex.py:8-374: same phi-function problem and sub-stepping as ``kiops``; every Krylov step needs ONE reduction
     (V[:j+1] @ V[j-1:j+1].T, pmex.py:168-176) from which the projection coefficients and, when it is safe, the norm of
@@ -356,7 +371,6 @@ def pmex(tau_out, A, u, tol=1e-7, delta=1.2, m_init=10, mmin=10, mmax=128, reuse
     kest = 2.0
     l = 0
     beta = nrm = 0.0
-    numpy.seterr(divide="ignore", invalid="ignore")
     while tau_now < tau_end:
         if j == 0:
             H[:, :] = 0.0

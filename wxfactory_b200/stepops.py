@@ -127,25 +127,36 @@ class VecOps:
         self.launches += 1
         return out
 
+    def _reduce(self, kind, x, y, slot):
+        self._chk(
+            self.lib.wxb_vec_reduce(x.numel(), kind, x.data_ptr(), y.data_ptr() if y is not None else None, self._small[slot : slot + 1].data_ptr(),
+                                    self._scratch.data_ptr(), _sp(self.torch, self.device)),
+            "wxb_vec_reduce",
+        )
+        self.launches += 2
+
     def asum_rows(self, U):
-        """1-norms of the rows of U (kiops.py:111-116; once per KIOPS call, on the few phi-function vectors)."""
-        a = U.abs().sum(dim=1)
+        """1-norms of the rows of U summed over ranks (kiops.py:111-116; once per call, on the few phi-function vectors)."""
+        k = U.shape[0]
+        for i in range(k):
+            self._reduce(0, U[i], None, i)
+        a = self._small[:k]
         if self.world_size > 1:
             import torch.distributed as dist
 
             dist.all_reduce(a, group=self.group)
-        return a.cpu().numpy()
+        return a.cpu().numpy().copy()
 
     def max_rel_change(self, update, x):
-        """max |update / x| over x != 0 (stagnation test of fgmres.py:257-262, once per restart cycle)."""
-        nz = x != 0
-        loc = float((update[nz] / x[nz]).abs().max()) if bool(nz.any()) else -1.0  # -1: no non-zero entry on this rank
-        if self.world_size > 1:  # one answer on every rank (the reference takes the local maximum: ranks could part ways)
+        """max |update / x| over x != 0 (stagnation test of fgmres.py:257-262, once per restart cycle); the maximum over
+        ranks, so that every rank takes the same decision (the reference takes the local one)."""
+        self._reduce(1, x, update, 0)
+        t = self._small[:1]
+        if self.world_size > 1:
             import torch.distributed as dist
 
-            t = self.torch.full((1,), loc, dtype=self.torch.float64, device=self.device)
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-            loc = float(t.item())
+        loc = float(t.item())
         return loc if loc >= 0.0 else math.inf
 
     def scale(self, x, s, out=None):
