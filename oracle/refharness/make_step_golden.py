@@ -10,7 +10,7 @@ Everything is produced by the UNMODIFIED reference run here (harness.py):
 * ``tests/golden/krylov_small.npz``       the reference's ``fgmres`` (wx_factory/solvers/fgmres.py:98-281) on a seeded
   dense system and ``kiops`` (wx_factory/solvers/kiops.py:10-346) on a seeded matrix with three phi-vectors:
   inputs, solutions, iteration counts, residual history / stats;
-* ``tests/golden/steps_<integrator>_<case>.npz``  final state after N steps of the reference's own ``Ros2`` +
+* ``tests/golden/steps_<integrator>_<case>.npz``  final state after N = 10 steps of the reference's own ``Ros2`` +
   fgmres, ``Epi(2)`` + kiops, ``Epi(3)`` + kiops and ``Epi(3)`` + pmex (config/case6.ini) around its own RHS on 6 thread-ranks (the drift report of
   SURVEY.md section 8d), with the per-step solver iteration counts.
 """
@@ -39,12 +39,12 @@ FILTER_CASES = {
 
 # name: (integrator, config, steps, dt fraction, config overrides)
 STEP_CASES = {
-    "ros2_dcmip21": ("ros2", "dcmip21", 3, 0.2, {"gmres_restart": 20, "tolerance": 1e-7}),
+    "ros2_dcmip21": ("ros2", "dcmip21", 10, 0.2, {"gmres_restart": 20, "tolerance": 1e-7}),
     # jacobian_method = fd: the finite-difference JVP of the north star (the schema default is the complex step)
-    "epi2_dcmip31": ("epi2", "dcmip31", 3, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
-    "epi3_dcmip21": ("epi3", "dcmip21", 4, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
+    "epi2_dcmip31": ("epi2", "dcmip31", 10, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
+    "epi3_dcmip21": ("epi3", "dcmip21", 10, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
     # config/case6.ini as shipped: Epi(3) + PMEX on the shallow-water Rossby-Haurwitz wave (BASELINE configs[0])
-    "epi3_case6": ("epi3", "case6", 4, 1.0, {"tolerance": 1e-7, "exponential_solver": "pmex", "jacobian_method": "fd"}),
+    "epi3_case6": ("epi3", "case6", 10, 1.0, {"tolerance": 1e-7, "exponential_solver": "pmex", "jacobian_method": "fd"}),
 }
 
 

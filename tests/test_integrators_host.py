@@ -56,8 +56,8 @@ def test_implicit_and_exponential_steps_follow_reference(name, case, kind):
     assert its == [int(i) for i in g["iterations"]]  # same Krylov iterations per step as the reference
     # the solvers stop at tolerance 1e-7; two implementations agree far below that because they follow the same
     # iterates: what differs is the rounding of the reductions, amplified by 1/eps ~ 2900 in the FD products and by the
-    # incomplete orthogonalisation (measured here: ros2 2e-13, epi2 1.9e-10, epi3 1e-11)
+    # incomplete orthogonalisation (measured here after 10 steps: ros2 8.9e-12, epi2 1.3e-10, epi3 7.9e-10)
     # epi3_case6 (Epi(3) + PMEX at the config's full dt = 1800 s) is conditioned at the solver tolerance itself: changing
     # the initial state by 2e-16 relative moves this result by 1.4e-8 (same code, same machine), so the bound there is the
-    # solver tolerance 1e-7 (measured 1.3e-8)
-    assert _rel(Q.numpy(), g["QN"]) <= (1e-11 if kind == "ros2" else 1e-7 if name == "epi3_case6" else 1e-8)
+    # solver tolerance 1e-7 (measured 3.3e-8 after 10 steps)
+    assert _rel(Q.numpy(), g["QN"]) <= (1e-10 if kind == "ros2" else 1e-7 if name == "epi3_case6" else 1e-8)

@@ -17,6 +17,7 @@
 // The vector kernels are free functions of the C ABI (no handle): Krylov vectors are plain device arrays.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "wxb_internal.cuh"
 
@@ -138,26 +139,57 @@ __global__ void __launch_bounds__(VEC_THREADS) nonfinite_kernel(long long n, con
 // ------------------------------------------------------------------------------------------------------
 // multi-dot, stage 1: partial[block][i][c] = sum over the block's grid-stride entries of V[i][x] W[c][x]
 // (m <= MD_ROWS rows per launch, K = 1 or 2 right-hand vectors); warp-shuffle + shared-memory reduction in a fixed order
-template <int K>
+// ROWS = rows per pass: 8, or 2 for the dots / norms / short incomplete orthogonalisations of KIOPS, where the entry loop
+// is unrolled by 4 instead so that enough loads are in flight per thread.
+template <int K, int VEC, int ROWS>
 __global__ void __launch_bounds__(VEC_THREADS) multidot_partial(long long n, int m, const double* __restrict__ V, long long ldv,
                                                                const double* __restrict__ W, long long ldw, double* __restrict__ partial,
                                                                int mtot, int row0) {
+    constexpr int MD_ROWS = ROWS;
+    constexpr int UNR = ROWS <= 2 ? 4 : 1;
     double acc[MD_ROWS][K];
 #pragma unroll
     for (int i = 0; i < MD_ROWS; ++i)
 #pragma unroll
         for (int c = 0; c < K; ++c) acc[i][c] = 0.0;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long x = blockIdx.x * (long long)blockDim.x + threadIdx.x; x < n; x += stride) {
-        double w[K];
+    const long long gid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (VEC == 2) {  // rows 16-byte aligned: two entries per 128-bit load (half the load instructions per byte)
+        const long long nv = n >> 1;
+#pragma unroll UNR
+        for (long long x = gid; x < nv; x += stride) {
+            double2 w[K];
 #pragma unroll
-        for (int c = 0; c < K; ++c) w[c] = W[c * ldw + x];
+            for (int c = 0; c < K; ++c) w[c] = reinterpret_cast<const double2*>(W + c * ldw)[x];
 #pragma unroll
-        for (int i = 0; i < MD_ROWS; ++i) {
-            if (i < m) {
-                const double v = V[i * ldv + x];
+            for (int i = 0; i < MD_ROWS; ++i) {
+                if (i < m) {
+                    const double2 v = reinterpret_cast<const double2*>(V + i * ldv)[x];
 #pragma unroll
-                for (int c = 0; c < K; ++c) acc[i][c] = fma(v, w[c], acc[i][c]);
+                    for (int c = 0; c < K; ++c) acc[i][c] = fma(v.y, w[c].y, fma(v.x, w[c].x, acc[i][c]));
+                }
+            }
+        }
+        if ((n & 1) && gid == 0) {  // odd length: the last entry
+#pragma unroll
+            for (int i = 0; i < MD_ROWS; ++i)
+                if (i < m)
+#pragma unroll
+                    for (int c = 0; c < K; ++c) acc[i][c] = fma(V[i * ldv + n - 1], W[c * ldw + n - 1], acc[i][c]);
+        }
+    } else {
+#pragma unroll UNR
+        for (long long x = gid; x < n; x += stride) {
+            double w[K];
+#pragma unroll
+            for (int c = 0; c < K; ++c) w[c] = W[c * ldw + x];
+#pragma unroll
+            for (int i = 0; i < MD_ROWS; ++i) {
+                if (i < m) {
+                    const double v = V[i * ldv + x];
+#pragma unroll
+                    for (int c = 0; c < K; ++c) acc[i][c] = fma(v, w[c], acc[i][c]);
+                }
             }
         }
     }
@@ -347,13 +379,23 @@ int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, cons
                      double* scratch_dev, void* stream) {
     if (n <= 0 || m <= 0 || m > WXB_VEC_MAX_ROWS || (k != 1 && k != 2) || !V || !W || !out_dev || !scratch_dev) return WXB_EINVAL;
     cudaStream_t s = (cudaStream_t)stream;
-    const int blocks = grid_for(n);
-    for (int row0 = 0; row0 < m; row0 += MD_ROWS) {
-        const int mm = m - row0 < MD_ROWS ? m - row0 : MD_ROWS;
-        if (k == 1)
-            multidot_partial<1><<<blocks, VEC_THREADS, 0, s>>>(n, mm, V + row0 * ldv, ldv, W, ldw, scratch_dev, m, row0);
-        else
-            multidot_partial<2><<<blocks, VEC_THREADS, 0, s>>>(n, mm, V + row0 * ldv, ldv, W, ldw, scratch_dev, m, row0);
+    // 128-bit loads when every row starts on a 16-byte boundary (WXB_VEC_NOVEC2=1 forces the scalar kernel)
+    static const bool novec = getenv("WXB_VEC_NOVEC2") && atoi(getenv("WXB_VEC_NOVEC2"));
+    const bool vec2 = !novec && ((uintptr_t)V % 16 == 0) && ((uintptr_t)W % 16 == 0) && (ldv % 2 == 0) && (ldw % 2 == 0 || k == 1);
+    const int blocks = grid_for(vec2 ? (n + 1) / 2 : n);
+    const int rows = m <= 2 ? 2 : MD_ROWS;
+    for (int row0 = 0; row0 < m; row0 += rows) {
+        const int mm = m - row0 < rows ? m - row0 : rows;
+        const double* Vp = V + row0 * ldv;
+#define WXB_MD_LAUNCH(KK, VV, RR) multidot_partial<KK, VV, RR><<<blocks, VEC_THREADS, 0, s>>>(n, mm, Vp, ldv, W, ldw, scratch_dev, m, row0)
+        if (rows == 2) {
+            if (vec2) { if (k == 1) WXB_MD_LAUNCH(1, 2, 2); else WXB_MD_LAUNCH(2, 2, 2); }
+            else      { if (k == 1) WXB_MD_LAUNCH(1, 1, 2); else WXB_MD_LAUNCH(2, 1, 2); }
+        } else {
+            if (vec2) { if (k == 1) WXB_MD_LAUNCH(1, 2, MD_ROWS); else WXB_MD_LAUNCH(2, 2, MD_ROWS); }
+            else      { if (k == 1) WXB_MD_LAUNCH(1, 1, MD_ROWS); else WXB_MD_LAUNCH(2, 1, MD_ROWS); }
+        }
+#undef WXB_MD_LAUNCH
     }
     multidot_final<<<(m * k + 127) / 128, 128, 0, s>>>(blocks, m * k, scratch_dev, out_dev);
     return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
