@@ -44,6 +44,8 @@ STEP_CASES = {
     "epi2_dcmip31": ("epi2", "dcmip31", 10, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
     "epi3_dcmip21": ("epi3", "dcmip21", 10, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
     # config/case6.ini as shipped: Epi(3) + PMEX on the shallow-water Rossby-Haurwitz wave (BASELINE configs[0])
+    # a higher-order multistep member (two previous steps, phi_1..phi_3): exercises the history deque and the coefficient rows
+    "epi4_dcmip21": ("epi4", "dcmip21", 6, 0.2, {"tolerance": 1e-7, "exponential_solver": "kiops", "jacobian_method": "fd"}),
     "epi3_case6": ("epi3", "case6", 10, 1.0, {"tolerance": 1e-7, "exponential_solver": "pmex", "jacobian_method": "fd"}),
 }
 
@@ -79,8 +81,10 @@ def make_solvers():
         b = rng.standard_normal(n)
         x0 = rng.standard_normal(n)
         out = {"fg_M": M, "fg_b": b, "fg_x0": x0}
-        for tag, restart in (("a", 20), ("b", 6)):
-            x, nr, nb, nit, flag, res = fgmres(lambda v: M @ v, b, x0=x0, tol=1e-10, restart=restart, maxiter=50, device=dev)
+        dM = numpy.diag(M).copy()
+        for tag, restart in (("a", 20), ("b", 6), ("h", 10), ("p", 8)):  # h: Hegedus rescaling, p: Jacobi-preconditioned
+            x, nr, nb, nit, flag, res = fgmres(lambda v: M @ v, b, x0=x0, tol=1e-10, restart=restart, maxiter=50, device=dev, hegedus=(tag == "h"),
+                                               preconditioner=(lambda v: v / dM) if tag == "p" else None)
             out[f"fg_x_{tag}"] = x
             out[f"fg_meta_{tag}"] = numpy.array([nr, nb, nit, flag, restart], dtype=float)
             out[f"fg_res_{tag}"] = numpy.array([r[0] for r in res])

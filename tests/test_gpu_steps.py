@@ -23,7 +23,8 @@ def _rel(a, b):
     return numpy.linalg.norm(a - b) / numpy.linalg.norm(b)
 
 
-@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi3_case6", "case6", "epi3")])
+@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi4_dcmip21", "dcmip21", "epi4"),
+                                             ("epi3_case6", "case6", "epi3")])
 def test_steps_follow_reference(golden, name, case, kind):
     import torch
 

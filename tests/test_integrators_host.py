@@ -38,7 +38,8 @@ def test_tvdrk3_bit_identical_to_reference_trajectory():
     assert numpy.array_equal(Q.numpy(), g["QN"])  # the oracle is bit-identical to the reference, the stage algebra too
 
 
-@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi3_case6", "case6", "epi3")])
+@pytest.mark.parametrize("name,case,kind", [("ros2_dcmip21", "dcmip21", "ros2"), ("epi2_dcmip31", "dcmip31", "epi2"), ("epi3_dcmip21", "dcmip21", "epi3"), ("epi4_dcmip21", "dcmip21", "epi4"),
+                                             ("epi3_case6", "case6", "epi3")])
 def test_implicit_and_exponential_steps_follow_reference(name, case, kind):
     path = os.path.join(GOLDEN, f"steps_{name}.npz")
     g = numpy.load(path)

@@ -20,9 +20,11 @@ def _t(a):
 def test_fgmres_reproduces_reference_iterations_and_solution():
     M = G["fg_M"]
     A = lambda v: _t(M @ v.numpy())  # noqa: E731
-    for tag in ("a", "b"):
+    dM = numpy.diag(M).copy()
+    for tag in ("a", "b", "h", "p"):  # h: Hegedus rescaling of the initial guess (fgmres.py:166-172), p: Jacobi preconditioner
         nr, nb, nit, flag, restart = G[f"fg_meta_{tag}"]
-        x, norm_r, norm_b, niter, fl, res = fgmres(A, _t(G["fg_b"]), x0=_t(G["fg_x0"]), tol=1e-10, restart=int(restart), maxiter=50, ops=CpuVecOps())
+        x, norm_r, norm_b, niter, fl, res = fgmres(A, _t(G["fg_b"]), x0=_t(G["fg_x0"]), tol=1e-10, restart=int(restart), maxiter=50, ops=CpuVecOps(),
+                                                   hegedus=(tag == "h"), preconditioner=(lambda v: _t(v.numpy() / dM)) if tag == "p" else None)
         assert (niter, fl) == (int(nit), int(flag))
         assert abs(norm_b - nb) <= 1e-13 * nb
         want = G[f"fg_res_{tag}"]

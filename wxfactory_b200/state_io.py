@@ -60,7 +60,6 @@ def gather_state(rhs, local, group=None):
     loc = loc.reshape(-1)
     if rhs.nranks == 1:
         return scatter_back(prob, rhs.part, loc, numpy.empty(prob.state_shape))
-    import torch
     import torch.distributed as dist
 
     pieces = [None] * rhs.nranks if rhs.rank == 0 else None
@@ -74,7 +73,6 @@ def gather_state(rhs, local, group=None):
             prob.nh, prob.nz if euler else 1, prob.n, prob.bnd_sn, prob.bnd_we, nranks=rhs.nranks, rank=r,
             num_var=rhs.num_trace, nfaces=6 if euler else 4, trace_layout="element" if euler else "field")
         scatter_back(prob, part, piece, out)
-    del torch
     return out
 
 
