@@ -82,6 +82,24 @@
 #ifndef WXB_SYM
 #define WXB_SYM 1           // fields 1: Rusanov flux written in (own, facing) form without sorting the states into L / R
 #endif
+// elements per block of euler_traces; its lines are spread over ALL threads of the block.  With one 64-thread element per
+// block at n = 4 the 48 lines fill one warp and half of the other; 4 elements per block fill 6 warps of 8 completely but
+// measured slower on B200 (traces 0.251 vs 0.230 ms, profiles/r01_variants_teb.log): kept at the main kernel's values
+#ifndef WXB_TEB2
+#define WXB_TEB2 8
+#endif
+#ifndef WXB_TEB3
+#define WXB_TEB3 4
+#endif
+#ifndef WXB_TEB4
+#define WXB_TEB4 1
+#endif
+#ifndef WXB_TEB5
+#define WXB_TEB5 1
+#endif
+#ifndef WXB_TEB6
+#define WXB_TEB6 1
+#endif
 #ifndef WXB_TR_MINB
 #define WXB_TR_MINB 0       // resident blocks per SM euler_traces is compiled for (0: no register cap)
 #endif
@@ -127,6 +145,8 @@ struct Cfg {
     // elements per block: aim for ~256 threads
     static constexpr int EB = (N == 2) ? WXB_EB2 : (N == 3) ? WXB_EB3 : (N == 4) ? WXB_EB4 : (N == 5) ? WXB_EB5 : WXB_EB6;
     static constexpr int THREADS = EB * P;
+    static constexpr int TEB = (N == 2) ? WXB_TEB2 : (N == 3) ? WXB_TEB3 : (N == 4) ? WXB_TEB4 : (N == 5) ? WXB_TEB5 : WXB_TEB6;  // euler_traces
+    static constexpr int TTHREADS = TEB * P;
     // resident blocks per SM the main kernel is compiled for (register budget = 65536 / (THREADS * MINB))
     static constexpr int MINB = (N == 2) ? WXB_MINB2 : (N == 3) ? WXB_MINB3 : (N == 4) ? WXB_MINB4 : (N == 5) ? WXB_MINB5 : WXB_MINB6;
     // offsets into the operator block
@@ -204,20 +224,22 @@ __device__ __forceinline__ void line_of(int d, int pt, int& base, int& step) {
 template <int N>
 __global__ void
 #if WXB_TR_MINB
-__launch_bounds__(Cfg<N>::THREADS, WXB_TR_MINB)
+__launch_bounds__(Cfg<N>::TTHREADS, WXB_TR_MINB)
 #else
-__launch_bounds__(Cfg<N>::THREADS)
+__launch_bounds__(Cfg<N>::TTHREADS)
 #endif
 euler_traces(const EvalArgs a) {
     using C = Cfg<N>;
-    constexpr int P = C::P, F = C::F, EB = C::EB;
+    constexpr int P = C::P, F = C::F, EB = C::TEB;
     __shared__ double s_ext[2 * N];
     __shared__ double s_q[EB][5][P];  // rho u1, rho u2, rho w, log(rho), log(rho theta)
+    __shared__ int s_e[EB];
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
     const int e = element_of(a, blockIdx.x * EB + le);  // all elements, or those of a.elist (chunked host path)
     const bool active = e >= 0;
     if (threadIdx.x < 2 * N) s_ext[threadIdx.x] = a.ops[threadIdx.x];
+    if (node == 0) s_e[le] = e;
     if (active) {
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
         double x[NVAR];  // all loads first: the conditional store below must not fence them
@@ -240,8 +262,8 @@ euler_traces(const EvalArgs a) {
         s_q[le][4][node] = log(x[4]);
     }
     __syncthreads();
-    if (!active) return;
 #if WXB_TRACE_MAP
+    if (!active) return;
     // 6F trace points per element, one (line, side) per thread and round: all lanes of a warp carry a point (with both
     // sides per thread the 3F lines fill only 3/4 of the block's lanes, and the per-point exp/reciprocal work dominates)
     for (int tp = node; tp < 6 * F; tp += P) {
@@ -255,15 +277,19 @@ euler_traces(const EvalArgs a) {
         for (int v = 0; v < NTR; ++v) t[v * F] = o[v];
     }
 #else
-    // 3F lines per element; each yields the min-side and the max-side face value (same arithmetic per side as
-    // extrap_line, which euler_main uses for the element's own side)
-    for (int ln = node; ln < 3 * F; ln += P) {
+    // 3F lines per element, each yields the min-side and the max-side face value (same arithmetic per side as
+    // extrap_line, which the TMA-staged euler_main uses for the element's own side); the block's EB*3F lines are spread
+    // over all its threads
+    for (int lt = threadIdx.x; lt < EB * 3 * F; lt += EB * P) {
+        const int el = lt / (3 * F), ln = lt % (3 * F);
+        const int e2 = s_e[el];
+        if (e2 < 0) continue;
         const int d = ln / F, pt = ln % F;
         int base, step;
         line_of<N>(d, pt, base, step);
         double lo[NTR], hi[NTR];
-        extrap_line2<N>(s_ext, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, lo, hi);
-        double* t = a.trace + (((long long)e * 6 + 2 * d) * NTR) * F + pt;  // [E][face][field][F]
+        extrap_line2<N>(s_ext, &s_q[el][0][0], P, &s_q[el][3][0], &s_q[el][4][0], base, step, lo, hi);
+        double* t = a.trace + (((long long)e2 * 6 + 2 * d) * NTR) * F + pt;  // [E][face][field][F]
 #pragma unroll
         for (int v = 0; v < NTR; ++v) {
             t[v * F] = lo[v];
@@ -860,8 +886,8 @@ template <int N>
 int launch_traces(const EvalArgs& a, cudaStream_t s) {
     const int ne = a.elist ? a.nelist : a.E;
     if (ne == 0) return 0;
-    const int blocks = (ne + Cfg<N>::EB - 1) / Cfg<N>::EB;
-    euler_traces<N><<<blocks, Cfg<N>::THREADS, 0, s>>>(a);
+    const int blocks = (ne + Cfg<N>::TEB - 1) / Cfg<N>::TEB;
+    euler_traces<N><<<blocks, Cfg<N>::TTHREADS, 0, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 template <int N>
