@@ -99,6 +99,23 @@ def make_solvers():
             w, stats = pmex(taus, lambda v: J @ v, u, tol=1e-9, device=dev, **kw)
             out[f"pm_w_{tag}"] = w
             out[f"pm_stats_{tag}"] = numpy.array([float(s) for s in stats])
+        # the reference's own unit-test inputs (tests/unit/solvers/test_kiops.py, test_pmex.py, test_fgmres.py:
+        # random.Random(5646459), 64 x 64 entries uniform in [-1000, 1000], identity matvec for the phi solvers)
+        import random
+
+        rnd = random.Random(5646459)
+        U = numpy.array([[rnd.uniform(-1000.0, 1000.0) for _ in range(64)] for _ in range(64)])
+        out["ut_U"] = U
+        w, stats = kiops([1.0], lambda v: v, U, 1e-7, device=dev)
+        out["ut_kiops_w"], out["ut_kiops_stats"] = w, numpy.array([float(s) for s in stats])
+        w, stats = pmex([1.0], lambda v: v, U, 1e-7, device=dev)
+        out["ut_pmex_w"], out["ut_pmex_stats"] = w, numpy.array([float(s) for s in stats])
+        rnd = random.Random(5646459)
+        bv = numpy.array([rnd.uniform(-1000.0, 1000.0) for _ in range(64)])
+        Am = numpy.array([[rnd.uniform(-1000.0, 1000.0) for _ in range(64)] for _ in range(64)])
+        x, nr, nb, nit, flag, res = fgmres(lambda v: Am @ v, bv, tol=1e-7, device=dev)
+        out["ut_fg_b"], out["ut_fg_A"], out["ut_fg_x"] = bv, Am, x
+        out["ut_fg_meta"] = numpy.array([nr, nb, nit, flag], dtype=float)
         return out
 
     out = harness.run_ranks(1, work)[0]
