@@ -62,3 +62,25 @@ def test_restart_helpers_single_rank(golden, tmp_path):
     assert os.path.basename(name) == os.path.basename(FILE).replace("00000007", "00000003")
     loc, content = state_io.read_restart(rhs, name)
     assert numpy.array_equal(loc, local_state(prob, part, ex["Q0"])) and content.startswith("[General]")
+
+
+def test_save_load_works_like_the_reference_unit_test(tmp_path):
+    """tests/unit/output/test_state.py::test_save_load_works of the reference, replayed: a seeded 5-vector
+    (random.Random(5646459), uniform in [-10, 10]) and an INI text survive save_state / load_state unchanged."""
+    import random
+
+    rnd = random.Random(5646459)
+    arr = numpy.array([rnd.uniform(-10, 10) for _ in range(5)])
+    ini = "[General]\nequations = euler\n\n[Grid]\nnum_solpts = 4\n"
+    out = tmp_path / "test_state_data"
+    state_io.save_state(arr, ini, str(out))
+    data, version, content = state_io.load_state(str(out))
+    assert data.ndim == 1 and data.shape[0] == 5
+    assert all(arr[i] == data[i] for i in range(5))
+    assert version == state_io.STATE_VERSION
+    import configparser
+
+    a, b = configparser.ConfigParser(), configparser.ConfigParser()
+    a.read_string(ini)
+    b.read_string(content)
+    assert {s: dict(a[s]) for s in a.sections()} == {s: dict(b[s]) for s in b.sections()}
