@@ -75,21 +75,54 @@ class Integrator:
 
 class Tvdrk3(Integrator):
     """SSP-RK3 (tvdrk3.py:7-20).  Each stage is one RHS evaluation + one fused combination whose roundings are
-    those of the reference's numpy expressions."""
+    those of the reference's numpy expressions.
 
-    def __init__(self, param, rhs, **kwargs):
+    ``graph=True`` (single-rank ``RhsB200`` only): the 9 launches of a step (3 x traces + main, 3 combinations) are
+    captured once into a CUDA graph and replayed -- for small grids, where a step is launch-bound.  The graph is
+    re-captured when ``dt`` or the state size changes.  While it is in use the handle's per-evaluation timing ring holds
+    events recorded inside the graph: ``RhsB200.timing_history`` is not available for those evaluations."""
+
+    def __init__(self, param, rhs, graph=False, **kwargs):
         super().__init__(param, rhs, **kwargs)
         self.rhs = rhs
+        self.graph = bool(graph)
+        self._g = None
+        if self.graph and not (isinstance(self.rhs_obj, RhsB200) and self.rhs_obj.nranks == 1):
+            raise ValueError("graph=True needs a single-rank RhsB200")
 
-    def __step__(self, Q, dt):
+    def _stages(self, q, dt, f):
         o = self.ops
-        q = Q.reshape(-1)
-        f = self.rhs_obj
         q1 = o.lincomb3(1.0, q, 0.0, None, 1.0, f(q), dt)                           # Q + rhs(Q)*dt
         q2 = o.lincomb3(0.75, q, 0.25, q1, 0.25, f(q1), dt)                         # 0.75 Q + 0.25 Q1 + 0.25 rhs(Q1) dt
-        qn = o.lincomb3(1.0 / 3.0, q, 2.0 / 3.0, q2, 2.0 / 3.0, f(q2), dt, out=q1)  # 1/3 Q + 2/3 Q2 + 2/3 rhs(Q2) dt
+        return o.lincomb3(1.0 / 3.0, q, 2.0 / 3.0, q2, 2.0 / 3.0, f(q2), dt, out=q1)  # 1/3 Q + 2/3 Q2 + 2/3 rhs(Q2) dt
+
+    def _capture(self, q, dt):
+        r = self.rhs_obj
+        torch = r._tm()
+        f = lambda x: r._eval_device(x, None, None, 0.0, 0.0, -1)  # noqa: E731  (no timing queries inside a capture)
+        gq = q.clone()
+        side = torch.cuda.Stream(device=q.device)
+        side.wait_stream(torch.cuda.current_stream(q.device))
+        with torch.cuda.stream(side):  # one eager pass on a side stream: allocations and lazy set-up happen here
+            self._stages(gq, dt, f)
+        torch.cuda.current_stream(q.device).wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = self._stages(gq, dt, f)
+        r._have_timing = False  # the ring's latest events live in the graph
+        self._g = (g, gq, out, float(dt), q.numel())
+
+    def __step__(self, Q, dt):
+        q = Q.reshape(-1)
         self.solver_info = SolverInfo(total_num_it=1)
-        return qn.view(Q.shape)
+        if self.graph:
+            if self._g is None or self._g[3] != float(dt) or self._g[4] != q.numel():
+                self._capture(q, dt)
+            g, gq, out, _, _ = self._g
+            gq.copy_(q)
+            g.replay()
+            return out.clone().view(Q.shape)
+        return self._stages(q, dt, self.rhs_obj).view(Q.shape)
 
 
 class Ros2(Integrator):
