@@ -92,7 +92,8 @@ def make_solvers():
         J = -numpy.diag(numpy.linspace(0.1, 30.0, nk)) + 0.5 * rng.standard_normal((nk, nk)) / numpy.sqrt(nk)
         u = rng.standard_normal((3, nk))
         out["ki_J"], out["ki_u"] = J, u
-        for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True))):
+        for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True)),
+                              ("c", [-0.05], dict(m_init=10, mmin=10, mmax=64))):  # c: backward in time (sgn = -1), a single phi_0 vector below
             w, stats = kiops(taus, lambda v: J @ v, u, tol=1e-9, device=dev, **kw)
             out[f"ki_w_{tag}"] = w
             out[f"ki_stats_{tag}"] = numpy.array([float(s) for s in stats])

@@ -47,7 +47,8 @@ def test_fgmres_error_behaviour():
 def test_kiops_reproduces_reference_substeps_and_result():
     J = G["ki_J"]
     A = lambda v: _t(J @ v.numpy())  # noqa: E731
-    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True))):
+    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True)),
+                          ("c", [-0.05], dict(m_init=10, mmin=10, mmax=64))):  # c: backward in time
         w, stats = kiops(taus, A, _t(G["ki_u"]), tol=1e-9, ops=CpuVecOps(), **kw)
         want = G[f"ki_stats_{tag}"]
         assert [int(stats[i]) for i in (0, 1, 2, 3, 5)] == [int(want[i]) for i in (0, 1, 2, 3, 5)]
@@ -59,10 +60,19 @@ def test_kiops_reproduces_reference_substeps_and_result():
 def test_pmex_reproduces_reference_substeps_and_result():
     J = G["ki_J"]
     A = lambda v: _t(J @ v.numpy())  # noqa: E731
-    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True))):
+    for tag, taus, kw in (("a", [1.0], dict(m_init=10, mmin=10, mmax=64)), ("b", [0.25, 0.5, 1.0], dict(m_init=4, mmin=4, mmax=24, task1=True)),
+                          ("c", [-0.05], dict(m_init=10, mmin=10, mmax=64))):
         w, stats = pmex(taus, A, _t(G["ki_u"]), tol=1e-9, ops=CpuVecOps(), **kw)
         want = G[f"pm_stats_{tag}"]
         assert [int(stats[i]) for i in (0, 1, 2, 3, 5, 6)] == [int(want[i]) for i in (0, 1, 2, 3, 5, 6)]
         assert abs(stats[4] - want[4]) <= 1e-3 * want[4]
         ref = G[f"pm_w_{tag}"]
         assert numpy.linalg.norm(w.numpy() - ref) <= 1e-11 * numpy.linalg.norm(ref)
+
+
+def test_single_row_input_raises_like_the_reference():
+    import pytest
+
+    for solver in (kiops, pmex):
+        with pytest.raises(ValueError):  # the reference's zero-padding of a single row fails in numpy (kiops.py:78-81)
+            solver([1.0], lambda v: v, _t(G["ki_u"][:1]), ops=CpuVecOps())

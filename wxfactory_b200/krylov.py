@@ -180,10 +180,9 @@ def kiops(tau_out, A, u, tol=1e-7, m_init=10, mmin=10, mmax=128, iop=2, task1=Fa
     ppo, n = int(u.shape[0]), int(u.shape[1])
     p = ppo - 1
     if p == 0:
-        p = 1
-        u2 = ops.zeros(2, n)
-        u2[0].copy_(u[0])
-        u = u2
+        # the reference pads a single row with `row_stack((u, zeros(len(u))))` (kiops.py:78-81, pmex.py:53-56), which
+        # raises for any n > 1: same error here (the integrators always pass phi_0 and phi_1 rows)
+        raise ValueError("all the input array dimensions except for the concatenation axis must match exactly: u needs at least two rows")
     m = max(mmin, min(m_init, mmax))
     Vn = ops.zeros(mmax + 1, n)           # first n entries of every basis vector
     Va = numpy.zeros((mmax + 1, p))       # the augmented tails
@@ -337,10 +336,9 @@ def pmex(tau_out, A, u, tol=1e-7, delta=1.2, m_init=10, mmin=10, mmax=128, reuse
     ppo, n = int(u.shape[0]), int(u.shape[1])
     p = ppo - 1
     if p == 0:
-        p = 1
-        u2 = ops.zeros(2, n)
-        u2[0].copy_(u[0])
-        u = u2
+        # the reference pads a single row with `row_stack((u, zeros(len(u))))` (kiops.py:78-81, pmex.py:53-56), which
+        # raises for any n > 1: same error here (the integrators always pass phi_0 and phi_1 rows)
+        raise ValueError("all the input array dimensions except for the concatenation axis must match exactly: u needs at least two rows")
     step = krystep = ireject = reject = exps = reg_comm_nrm = 0
     sgn = float(numpy.sign(tau_out[-1]))
     tau_now, tau_end = 0.0, float(abs(tau_out[-1]))
