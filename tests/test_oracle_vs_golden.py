@@ -6,7 +6,7 @@ leaves room for a different BLAS summation order elsewhere."""
 import numpy
 import pytest
 
-from conftest import GOLDEN_NAMES
+from conftest import EXTRA_ORACLE_PINS, GOLDEN_NAMES
 from oracle import jvp_oracle
 
 TOL = 1e-14
@@ -16,7 +16,7 @@ def rel(a, b):
     return numpy.linalg.norm(a - b) / numpy.linalg.norm(b)
 
 
-@pytest.mark.parametrize("name", GOLDEN_NAMES)
+@pytest.mark.parametrize("name", GOLDEN_NAMES + EXTRA_ORACLE_PINS)
 def test_rhs_matches_reference(golden, name):
     prob, ex = golden(name)
     with numpy.errstate(all="ignore"):
@@ -25,7 +25,7 @@ def test_rhs_matches_reference(golden, name):
     assert rel(out, ex["rhs0"]) <= TOL
 
 
-@pytest.mark.parametrize("name", GOLDEN_NAMES)
+@pytest.mark.parametrize("name", GOLDEN_NAMES + EXTRA_ORACLE_PINS)
 def test_jvp_matches_reference(golden, name):
     prob, ex = golden(name)
     orc = jvp_oracle.make_oracle(prob)
