@@ -50,7 +50,8 @@ CONFIGS = {
     # tests/conftest.py), on grids shrunk to keep the fixtures small
     "case2": ("case2.ini", {"num_elements_horizontal": 4}, None),
     # (config/matsuno.ini, unsteady_zonal.ini and dcmip20.ini crash inside the reference's own initialisation here:
-    #  "too many values to unpack", a (4,6)->(12,) broadcast, apply_topography() missing arguments)
+    #  "too many values to unpack", a (4,6)->(12,) broadcast, apply_topography() missing arguments; config/case1.ini
+    #  gives a NaN right-hand side and config/dcmip11.ini / dcmip12.ini lack the mandatory lambda0)
 }
 
 
