@@ -6,7 +6,7 @@
   global_operations.py:15-34).  One object per (device, process group); every method enqueues on torch's current
   stream; only ``multidot`` / ``norm`` / ``nonfinite`` read a result back (the algorithms' own synchronisation points).
 
-No CPU fallback: the methods raise without a CUDA device.  (tests/vecops_numpy.py is a numpy stand-in used to check
+No CPU fallback: the methods raise without a CUDA device.  (tests/vecops_cpu.py is a CPU stand-in used to check
 the solvers' host logic on CPU; it is test infrastructure and is never imported from here.)
 """
 
