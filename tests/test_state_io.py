@@ -84,3 +84,17 @@ def test_save_load_works_like_the_reference_unit_test(tmp_path):
     a.read_string(ini)
     b.read_string(content)
     assert {s: dict(a[s]) for s in a.sections()} == {s: dict(b[s]) for s in b.sections()}
+
+
+def test_read_restart_rejects_a_state_of_the_wrong_shape(golden, tmp_path):
+    """OutputManager.load_state_from_file raises ValueError when the stored state does not fit the run
+    (wx_factory/output/output_manager.py:106-110): same here."""
+    import pytest
+
+    prob, ex = golden("dcmip21")
+    part = build_partition(prob.nh, prob.nz, prob.n, prob.bnd_sn, prob.bnd_we, nranks=1, rank=0, num_var=6, nfaces=6, trace_layout="element")
+    rhs = types.SimpleNamespace(prob=prob, part=part, nranks=1, rank=0, num_trace=6, local_state=lambda Q: local_state(prob, part, Q))
+    bad = tmp_path / "bad.npy"
+    state_io.save_state(numpy.zeros((6, 5, 2, 3, 3, 27)), "[General]\n", str(bad))
+    with pytest.raises(ValueError):
+        state_io.read_restart(rhs, str(bad))
