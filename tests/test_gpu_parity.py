@@ -134,13 +134,14 @@ def test_timings_vocabulary(rhs_cache):
     assert len(rhs.timings) >= 1 and all(t[2] > 0 for t in rhs.timings)
 
 
-def test_tma_staged_variant_matches_too():
-    """The TMA-staged variant of euler_main (WXB_KERNEL_OPTS=4, csrc/euler3d.cu) is selected per process: run the
-    device-path parity cases again in a child process with it switched on."""
+def test_split_path_matches_too():
+    """The Euler handles run the fused column-sweep kernel (csrc/euler_sweep.cu) by default; the traces + main pair of
+    csrc/euler3d.cu is selected per process with WXB_EULER_PATH=split: run the device-path parity cases again in a
+    child process with it switched on."""
     import subprocess
     import sys
 
-    env = dict(os.environ, WXB_KERNEL_OPTS="4")
+    env = dict(os.environ, WXB_EULER_PATH="split")
     here = os.path.abspath(__file__)
     r = subprocess.run(
         [sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k", "device_path or jvp_matches"],

@@ -92,7 +92,9 @@ def test_nonfinite_counts(ops):
     assert ops.nonfinite(x) == 3
 
 
-@pytest.mark.parametrize("m,k,n", [(1, 1, 10), (2, 1, 100_003), (3, 2, 5), (22, 2, 200_001), (64, 2, 50_000)])
+# 65 and 129 rows: PMEX asks for j + 1 <= mmax + 1 rows (pmex.py:168-176); VecOps.multidot walks the basis in chunks of
+# WXB_VEC_MAX_ROWS rows
+@pytest.mark.parametrize("m,k,n", [(1, 1, 10), (2, 1, 100_003), (3, 2, 5), (22, 2, 200_001), (64, 2, 50_000), (65, 2, 30_001), (129, 2, 9_999)])
 def test_multidot_matches_numpy_and_is_reproducible(ops, m, k, n):
     import torch
 

@@ -89,6 +89,27 @@ def _worker(rank, world, port, ok):
         good &= (total is None) if rank else bool(numpy.array_equal(total, ex["Q0"].reshape(prob.state_shape)))
         back = state_io.scatter_state(rhs, total)
         good &= bool(numpy.array_equal(back, mine))
+        # restart file: write on rank 0, read on every rank; a missing file or a state of the wrong shape raises on
+        # EVERY rank instead of leaving the others in the broadcast
+        import tempfile
+
+        tmp = os.path.join(tempfile.gettempdir(), f"wxb_state_gloo_{port}")
+        name = state_io.write_restart(rhs, mine, "[General]\n", tmp, 3, 1.0)
+        box = [name]
+        dist.broadcast_object_list(box, src=0)
+        got, content = state_io.read_restart(rhs, box[0])
+        good &= bool(numpy.array_equal(got, mine)) and content.strip() == "[General]"
+        for bad, exc in ((box[0] + ".missing", OSError), (None, ValueError)):
+            if bad is None:
+                bad = os.path.join(tmp, "wrong_shape.npy")
+                if rank == 0:
+                    state_io.save_state(numpy.zeros((6, 5, 1, 2, 2, 8)), "[General]\n", bad)
+                dist.barrier()
+            try:
+                state_io.read_restart(rhs, bad)
+                good = False
+            except exc:
+                pass
         ok[rank] = int(bool(good))
     finally:
         dist.destroy_process_group()

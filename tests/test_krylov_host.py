@@ -76,3 +76,31 @@ def test_single_row_input_raises_like_the_reference():
     for solver in (kiops, pmex):
         with pytest.raises(ValueError):  # the reference's zero-padding of a single row fails in numpy (kiops.py:78-81)
             solver([1.0], lambda v: v, _t(G["ki_u"][:1]), ops=CpuVecOps())
+
+
+def test_pmex_reaches_mmax_rows():
+    """PMEX's one reduction per Krylov step covers j + 1 rows with j up to mmax, i.e. one more row than the
+    basis size limit; the vector backend must take it (the CUDA backend walks the basis in chunks of WXB_VEC_MAX_ROWS
+    rows, tests/test_gpu_stepops.py).  A stiff operator at a tight tolerance drives the adaptive Krylov size to mmax."""
+    rng = numpy.random.default_rng(5)
+    n = 400
+    J = -numpy.diag(numpy.logspace(0, 4, n)) + 0.01 * rng.standard_normal((n, n))
+    u = numpy.vstack([rng.standard_normal(n), rng.standard_normal(n)])
+    seen = []
+
+    class Recording(CpuVecOps):
+        def multidot(self, V, m, W, k):
+            seen.append(m)
+            return super().multidot(V, m, W, k)
+
+    mmax = 16
+    w, stats = pmex([1.0], lambda v: _t(J @ v.numpy()), _t(u), tol=1e-7, m_init=8, mmin=8, mmax=mmax, ops=Recording())
+    assert max(seen) == mmax + 1
+    import scipy.linalg
+
+    # phi_0(J) u0 + phi_1(J) u1 through the augmented matrix exponential
+    A = numpy.zeros((n + 1, n + 1))
+    A[:n, :n] = J
+    A[:n, n] = u[1]
+    want = scipy.linalg.expm(A)[:n] @ numpy.concatenate([u[0], [1.0]])
+    assert numpy.linalg.norm(w.numpy()[0] - want) <= 1e-5 * numpy.linalg.norm(want)

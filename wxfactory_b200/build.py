@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libwxb200.so")
-SOURCES = ["wxb_api.cu", "euler3d.cu", "sw2d.cu", "stepops.cu"]
+SOURCES = ["wxb_api.cu", "euler3d.cu", "euler_sweep.cu", "sw2d.cu", "stepops.cu"]
 NVCC_FLAGS = [
     "-gencode",
     "arch=compute_100a,code=sm_100a",
@@ -50,6 +50,22 @@ def build(force=False, verbose=False):
     cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-lcudart"]
     subprocess.check_call(cmd)
     return LIB
+
+
+def build_if_stale():
+    """What capi.load() calls: rebuild when a source is newer than the library (so that tests and benches never run
+    stale kernels), one process at a time (ranks of a torchrun job start together).  WXB_NO_REBUILD=1 keeps whatever
+    library is there."""
+    if os.path.exists(LIB) and (os.environ.get("WXB_NO_REBUILD") == "1" or not _stale()):
+        return LIB
+    import fcntl
+
+    with open(os.path.join(HERE, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return build()  # returns at once if another process has just built it
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
 
 
 if __name__ == "__main__":

@@ -109,9 +109,7 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB
-    if not os.path.exists(path):
-        path = _build.build()
+    path = _build.build_if_stale()
     lib = ctypes.CDLL(path)
     vp, i32, i64, dbl = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
     lib.wxb_version.restype = i32

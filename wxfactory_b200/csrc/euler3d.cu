@@ -517,93 +517,39 @@ __device__ __forceinline__ void apply_xform(const EvalArgs& a, int flags, int al
 }
 
 // ------------------------------------------------------------------------------------------------------
-// TMA bulk copy + mbarrier (sm_90+/sm_100a): one instruction moves one 8P-byte element row global -> shared
-// memory asynchronously; completion is counted in bytes on an mbarrier.
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-    unsigned ok = 0;
-    while (!ok) {
-        asm volatile(
-            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
-            : "=r"(ok)
-            : "r"(smem_u32(bar)), "r"(parity)
-            : "memory");
-    }
-}
+// Rows of the per-element shared-memory area (each P doubles): 0-17 flux fields (d*6 + {F_rho, F_u1, F_u2, F_theta,
+// w_adv, w_pres}), 18 = log(Rd/p0 rho theta), 19 = sqrtG*rho.  A thread only ever writes its own node's column.
+constexpr int NFLUX = 20, RLOGP = 18, RSGRHO = 19;
+constexpr int R_CH = 0, R_SG = 27, R_H = 28, R_IDZ = 34;  // rows of the element's metric block [35][P] (wxb_api.cu)
+constexpr int NMETRIC = 35;
 
-// Rows of the per-element shared-memory area (each P doubles).
-//   as staged by TMA:   0-4 q | 5-31 Christoffel (27) | 32 sqrtG | 33-38 h (6) | 39 1/z_eta
-//   after the node pass: 0-4 q | 5-24 flux fields (d*6 + {F_rho, F_u1, F_u2, F_theta, w_adv, w_pres}; 23 = log p;
-//                        24 = sqrtG*rho) | 25 log rho | 26 log(rho theta) | 27-39 dead -> interface results
-// A thread only ever reads and overwrites its own node's column, so the reuse needs no extra barrier.
-constexpr int R_Q = 0, R_CH = 5, R_SG = 32, R_H = 33, R_IDZ = 39, NROWS = 40;
-constexpr int R_FL = 5, R_LRHO = 25, R_LRT = 26, R_FF = 27, NFLUX = 20;
-constexpr int NMETRIC = 35;  // rows 5..39 = one contiguous device block [35][E*P] (see wxb_api.cu)
-
-// STAGED: the element rows are 16-byte multiples (even n): node data and the neighbours' trace rows come in
-// through TMA bulk copies.  Otherwise (odd n) they are loaded directly.
 template <int N>
-constexpr bool can_stage() { return (Cfg<N>::P * 8) % 16 == 0 && (Cfg<N>::F * 8) % 16 == 0; }
-
-template <int N, bool STG>
-struct MainCfg {
-    static constexpr int P = Cfg<N>::P, F = Cfg<N>::F;
-    static constexpr bool STAGED = STG && can_stage<N>();
-    // direct mode keeps only the 20 flux rows in shared memory (own traces are read back from a.trace)
-    static constexpr int RFL = STAGED ? R_FL : 0, RLOGP = RFL + 18, RSGRHO = RFL + 19;
-    static constexpr int ROWS = STAGED ? NROWS : NFLUX;
-    // interface results (6 faces x NFF values x F) reuse the dead rows when they fit
-    static constexpr bool FF_ALIAS = STAGED && (NROWS - R_FF) * P >= 6 * NFF * F;
-    static constexpr int FF_OWN = FF_ALIAS ? 1 : 6 * NFF * F;
-    static constexpr int NBR = STAGED ? 6 * NTR : 1, NBE = STAGED ? Cfg<N>::EB : 1, NBF = STAGED ? F : 1;
-};
-
-template <int N, bool STG>
 struct MainSmem {
-    alignas(16) double st[MainCfg<N, STG>::ROWS][Cfg<N>::EB][Cfg<N>::P];  // row-major across the block's elements
-    alignas(16) double nb[MainCfg<N, STG>::NBR][MainCfg<N, STG>::NBE][MainCfg<N, STG>::NBF];  // facing traces [face*6+field][element][F]
-    double ff[Cfg<N>::EB][MainCfg<N, STG>::FF_OWN];
+    alignas(16) double st[NFLUX][Cfg<N>::EB][Cfg<N>::P];  // row-major across the block's elements
+    double ff[Cfg<N>::EB][6 * NFF * Cfg<N>::F];            // interface results (face*NFF + value, point)
     double op[Cfg<N>::NOPS];
     ElemInfo ei[Cfg<N>::EB];
     NbrRow nr[Cfg<N>::EB][6];
     FaceRow fr[Cfg<N>::EB][6];
-    unsigned long long bar[2];
 };
 
 // ------------------------------------------------------------------------------------------------------
 // main kernel: one thread per solution point, EB elements per block.
-//   phase 0  (STAGED) bulk copies bring the element's 40 node rows (barrier 0) and the 36 facing trace rows
-//            (barrier 1) into shared memory
-//   phase 1  per node: forcing, the flux fields of the three directions, log rho / log(rho theta)
-//   phase 2  per face point: own trace (same arithmetic as euler_traces), facing trace, Rusanov flux
-//   phase 3  per node: sum-factorised derivative + lift, assemble, epilogue
+//   interface pass  per face point: own trace, facing trace (pull table), Rusanov flux -> shared memory
+//   node pass       per node: forcing, the flux fields of the three directions -> shared memory
+//   assemble        per node: sum-factorised derivative + lift, epilogue
 // In JVP mode the state rows come from the perturbed state q + eps*v written by euler_traces (a.qp).
-template <int N, bool JVP, bool STG>
+template <int N, bool JVP>
 __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(const EvalArgs a) {
     using C = Cfg<N>;
-    using MC = MainCfg<N, STG>;
     constexpr int P = C::P, F = C::F, EB = C::EB;
-    constexpr bool STAGED = MC::STAGED;
-    constexpr bool USE_FR = N >= WXB_FR_MIN_N;  // per-face address table (direct mode)
+    constexpr bool USE_FR = N >= WXB_FR_MIN_N;  // per-face address table
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    using SM = MainSmem<N, STG>;
+    using SM = MainSmem<N>;
     SM& sm = *reinterpret_cast<SM*>(smem_raw);
     double* const s_op = sm.op;
 
     const int le = threadIdx.x / P, node = threadIdx.x % P;
-    const int ne = a.elist ? a.nelist : a.E;
     const int e = element_of(a, blockIdx.x * EB + le);
     const bool active = e >= 0;
     const double* const qsrc = JVP ? a.qp : a.q;
@@ -612,68 +558,15 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     if (active && node == 0) make_info(a, e, F, P, sm.ei[le]);
     if (active && node >= P - 6) {  // six other threads look the facing rows up (one table load each)
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NVAR);
-        if (STAGED || !USE_FR) sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
+        if (!USE_FR) sm.nr[le][node - (P - 6)] = nbr_row(a, e, ep.k, ep.c, ep.ny, node - (P - 6));
         else make_face_row(a, e, ep, node - (P - 6), F, sm.fr[le][node - (P - 6)]);
-    }
-    if (STAGED && threadIdx.x == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
     }
     __syncthreads();
     constexpr int RS = EB * P;  // distance between rows of one element
-    // interface result (face*7 + value, point): in the element's dead rows when they fit, else in its own array
-    auto ffp = [&](int fv, int pt) -> double* {
-        const int idx = fv * F + pt;
-        return MC::FF_ALIAS ? &sm.st[(MC::FF_ALIAS ? R_FF : 0) + idx / P][le][idx % P] : &sm.ff[le][MC::FF_ALIAS ? 0 : idx];
-    };
+    auto ffp = [&](int fv, int pt) -> double* { return &sm.ff[le][fv * F + pt]; };
 
-    // ---- phase 0: start the bulk copies ----
-    if (STAGED) {
-        const int nact = min(EB, ne - (int)blockIdx.x * EB);
-        if (threadIdx.x == 0) {
-            int nrows = 0;
-            for (int el = 0; el < nact; ++el)
-                nrows += 6 - (sm.ei[el].k == 0) - (sm.ei[el].k == a.nz - 1);
-            mbar_expect_tx(&sm.bar[0], (unsigned)(nact * NROWS * P * 8));
-            mbar_expect_tx(&sm.bar[1], (unsigned)(nrows * NTR * F * 8));
-        }
-        // One elected thread per barrier issues the copies (uniform control flow -> plain UBLKCP, no per-lane
-        // serialisation); rows of consecutive elements are contiguous in global memory, so a run of elements moves
-        // as one copy.
-        if (threadIdx.x == 0) {
-            for (int el = 0; el < nact; ++el) {  // the element's 35 metric rows are contiguous in global memory
-                const double* src = a.chris + (long long)sm.ei[el].e * (NMETRIC * P);
-                if (EB == 1) {
-                    bulk_g2s(&sm.st[R_CH][0][0], src, NMETRIC * P * 8, &sm.bar[0]);  // ... and in shared memory: one copy
-                } else {
-                    for (int row = R_CH; row < NROWS; ++row) bulk_g2s(&sm.st[row][el][0], src + (row - R_CH) * P, P * 8, &sm.bar[0]);
-                }
-            }
-            for (int el0 = 0; el0 < nact;) {  // ... and of consecutive state rows (same slab)
-                int L = 1;
-                while (el0 + L < nact && sm.ei[el0 + L].qoff == sm.ei[el0].qoff + (long long)L * P) ++L;
-                const double* src = qsrc + sm.ei[el0].qoff;
-                for (int row = 0; row < NVAR; ++row) bulk_g2s(&sm.st[row][el0][0], src + row * sm.ei[el0].vstride, L * P * 8, &sm.bar[0]);
-                el0 += L;
-            }
-        } else if (threadIdx.x == 32) {
-            for (int f = 0; f < 6; ++f) {
-                for (int el = 0; el < nact; ++el) {  // the 6 fields of a facing face are contiguous in global memory
-                    const NbrRow nr = sm.nr[el][f];
-                    if (nr.bc) continue;
-                    if (EB == 1) {
-                        bulk_g2s(&sm.nb[f * NTR][0][0], a.trace + nr.row0 * F, NTR * F * 8, &sm.bar[1]);
-                    } else {
-                        for (int v = 0; v < NTR; ++v) bulk_g2s(&sm.nb[f * NTR + v][el][0], a.trace + (nr.row0 + v) * F, F * 8, &sm.bar[1]);
-                    }
-                }
-            }
-        }
-    }
-
-    // ---- interface fluxes, 6F face points per element ----
-    auto do_faces = [&]() {
-        if (!active || (a.dbg & 1)) return;
+    // ---- interface fluxes, 6F face points per element (their registers die before the node pass) ----
+    if (active) {
         const ElemInfo& ei = sm.ei[le];
         for (int fp = node; fp < 6 * F; fp += P) {
             const int f = fp / F, pt = fp % F, d = f >> 1, side = f & 1;
@@ -681,19 +574,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             double own[NTR], nb[NTR], fm[4];
             int flags;
             bool bc;
-            if (STAGED) {
-                const NbrRow& nr = sm.nr[le][f];
-                bc = nr.bc;
-                flags = nr.flags;
-                const int pt2 = (flags & 1) ? kl * N + (N - 1 - al) : pt;
-                const double* m = ei.fm[d] + (side ? ei.fm_side[d] : 0) + pt;
-                fm[0] = m[0]; fm[1] = m[F]; fm[2] = m[2 * F]; fm[3] = m[3 * F];
-                int base, step;
-                line_of<N>(d, pt, base, step);
-                extrap_line<N>(s_op + side * N, &sm.st[R_Q + 1][le][0], RS, &sm.st[R_LRHO][le][0], &sm.st[R_LRT][le][0], base, step, own);
-#pragma unroll
-                for (int v = 0; v < NTR; ++v) nb[v] = bc ? own[v] : sm.nb[f * NTR + v][le][pt2];  // mirrored ghost (rhs_dfr.py:265-268)
-            } else if (!USE_FR) {  // low orders: a face table per element costs more than it saves (few points per face)
+            if (!USE_FR) {  // low orders: a face table per element costs more than it saves (few points per face)
                 const NbrRow& nr = sm.nr[le][f];
                 bc = nr.bc;
                 flags = nr.flags;
@@ -726,17 +607,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
 #pragma unroll
             for (int v = 0; v < NFF; ++v) *ffp(f * NFF + v, pt) = res[v];
         }
-    };
+    }
 
-    if (!STAGED) do_faces();  // direct mode: nothing to wait for, and its registers die before the node pass
-
-    // ---- phase 1: nodes ----
+    // ---- nodes ----
     const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
     double sg = 1.0, p = 1.0, gfac = 0.0, fo[3] = {0.0, 0.0, 0.0};
     long long qo = 0, vst = 0;
     double* const col = &sm.st[0][le][node];  // this node's column (rows RS apart)
-    if (STAGED) mbar_wait(&sm.bar[0], 0);
-    if (a.dbg & 2) return;
     if (active) {
         const ElemInfo& ei = sm.ei[le];
         qo = ei.qoff + node;
@@ -746,13 +623,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         const double* const mrow = a.chris + (long long)e * (NMETRIC * P) + node;
         double q[NVAR], h[6];
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) q[v] = STAGED ? col[(R_Q + v) * RS] : qsrc[qo + v * vst];
-        sg = STAGED ? col[R_SG * RS] : mrow[(R_SG - R_CH) * P];
+        for (int v = 0; v < NVAR; ++v) q[v] = qsrc[qo + v * vst];
+        sg = mrow[R_SG * P];
 #pragma unroll
-        for (int c = 0; c < 6; ++c) h[c] = STAGED ? col[(R_H + c) * RS] : mrow[(R_H - R_CH + c) * P];
-        gfac = STAGED ? col[R_IDZ * RS] : mrow[(R_IDZ - R_CH) * P];
-        double ch[STAGED ? 1 : 27];  // direct mode: all 27 Christoffel loads in flight together
-        if (!STAGED && !WXB_CH3) {
+        for (int c = 0; c < 6; ++c) h[c] = mrow[(R_H + c) * P];
+        gfac = mrow[R_IDZ * P];
+        double ch[27];  // all 27 Christoffel loads in flight together
+        if (!WXB_CH3) {
 #pragma unroll
             for (int c = 0; c < 27; ++c) ch[c] = mrow[c * P];
         }
@@ -773,8 +650,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             for (int i = 0; i < 3; ++i) {
                 double c[9];
 #pragma unroll
-                for (int m = 0; m < 9; ++m)
-                    c[m] = STAGED ? col[(R_CH + 9 * i + m) * RS] : (WXB_CH3 ? mrow[(9 * i + m) * P] : ch[STAGED ? 0 : 9 * i + m]);
+                for (int m = 0; m < 9; ++m) c[m] = WXB_CH3 ? mrow[(9 * i + m) * P] : ch[9 * i + m];
                 fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
                         c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
             }
@@ -786,7 +662,6 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             }
         }
         // pointwise fluxes of the three directions (pde_euler_cubesphere.py:72-124) -> own column
-        double* fl = col + MC::RFL * RS;
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
             const double ud = d == 0 ? u1 : (d == 1 ? u2 : w);
@@ -794,30 +669,21 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
             const double hd1 = d == 0 ? h[1] : (d == 1 ? h[3] : h[4]);
             const double hd2 = d == 0 ? h[2] : (d == 1 ? h[4] : h[5]);
             const double sgu = sg * ud;
-            fl[(d * 6 + 0) * RS] = sgu * q[0];
-            fl[(d * 6 + 1) * RS] = sgu * q[1] + sg * hd0 * p;
-            fl[(d * 6 + 2) * RS] = sgu * q[2] + sg * hd1 * p;
-            fl[(d * 6 + 3) * RS] = sgu * q[4];
-            fl[(d * 6 + 4) * RS] = sgu * q[3];
-            fl[(d * 6 + 5) * RS] = sg * hd2;
+            col[(d * 6 + 0) * RS] = sgu * q[0];
+            col[(d * 6 + 1) * RS] = sgu * q[1] + sg * hd0 * p;
+            col[(d * 6 + 2) * RS] = sgu * q[2] + sg * hd1 * p;
+            col[(d * 6 + 3) * RS] = sgu * q[4];
+            col[(d * 6 + 4) * RS] = sgu * q[3];
+            col[(d * 6 + 5) * RS] = sg * hd2;
         }
 #if WXB_FOLD_LOGP
-        col[MC::RLOGP * RS] = lg;  // log p = log p0 + gamma*lg (pde_euler_cubesphere.py:124); see O_DLP
+        col[RLOGP * RS] = lg;  // log p = log p0 + gamma*lg (pde_euler_cubesphere.py:124); see O_DLP
 #else
-        col[MC::RLOGP * RS] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
+        col[RLOGP * RS] = WXB_LOG_P0 + WXB_GAMMA * lg;  // log p (pde_euler_cubesphere.py:124) without a second log
 #endif
-        col[MC::RSGRHO * RS] = sg * rho;
-        if (STAGED) {  // for the element's own traces (phase 2)
-            col[R_LRHO * RS] = log(rho);
-            col[R_LRT * RS] = log(q[4]);
-        }
+        col[RSGRHO * RS] = sg * rho;
     }
     __syncthreads();
-    if (STAGED) {
-        mbar_wait(&sm.bar[1], 0);
-        do_faces();
-        __syncthreads();
-    }
     if (!active) return;
 
     // the epilogue's operands are requested now so that their latency hides behind the derivative
@@ -831,15 +697,15 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         }
     }
 
-    // ---- phase 3: interior derivative (sum-factorised) + lift (correction) ----
+    // ---- interior derivative (sum-factorised) + lift (correction) ----
     double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
         const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
         const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
         const int pt = d == 0 ? kk * N + jj : (d == 1 ? kk * N + ii : jj * N + ii);
-        const double* sfd = &sm.st[MC::RFL + d * 6][le][node - idx * step];
-        const double* slp = &sm.st[MC::RLOGP][le][node - idx * step];
+        const double* sfd = &sm.st[d * 6][le][node - idx * step];
+        const double* slp = &sm.st[RLOGP][le][node - idx * step];
         double dv[7] = {0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
         for (int m = 0; m < N; ++m) {
@@ -857,7 +723,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         if (WXB_FOLD_LOGP) dv[6] = WXB_GAMMA * dv[6] + s_op[C::O_KLP + idx];
 #pragma unroll
         for (int v = 0; v < 4; ++v) acc[v] += dv[v];
-        const double wpres = col[(MC::RFL + d * 6 + 5) * RS];
+        const double wpres = col[(d * 6 + 5) * RS];
         wacc += dv[4] + p * dv[5] + p * wpres * dv[6];
     }
 
@@ -895,32 +761,18 @@ int launch_main(const EvalArgs& a, cudaStream_t s) {
     const int ne = a.elist ? a.nelist : a.E;
     if (ne == 0) return 0;
     const int blocks = (ne + Cfg<N>::EB - 1) / Cfg<N>::EB;
-    const bool stg = can_stage<N>() && (a.dbg & 4);
-    if (stg) {
-        constexpr int smem = (int)sizeof(MainSmem<N, true>);
-        if (a.mode >= 0)
-            euler_main<N, true, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
-        else
-            euler_main<N, false, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
-    } else {
-        constexpr int smem = (int)sizeof(MainSmem<N, false>);
-        if (a.mode >= 0)
-            euler_main<N, true, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
-        else
-            euler_main<N, false, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
-    }
+    constexpr int smem = (int)sizeof(MainSmem<N>);
+    if (a.mode >= 0)
+        euler_main<N, true><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
+    else
+        euler_main<N, false><<<blocks, Cfg<N>::THREADS, smem, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 template <int N>
 int configure_main() {
-    cudaError_t e[4];
-    e[0] = cudaFuncSetAttribute(euler_main<N, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, true>));
-    e[1] = cudaFuncSetAttribute(euler_main<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, true>));
-    e[2] = cudaFuncSetAttribute(euler_main<N, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, false>));
-    e[3] = cudaFuncSetAttribute(euler_main<N, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N, false>));
-    for (auto x : e)
-        if (x != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(euler_main<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N>)) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(euler_main<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MainSmem<N>)) != cudaSuccess) return -1;
     return 0;
 }
 

@@ -7,6 +7,7 @@
 #include <new>
 #include <vector>
 
+#include "fastmath.cuh"
 #include "wxb_internal.cuh"
 
 namespace {
@@ -217,16 +218,62 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     UP(h->d_xform, A->xform, (size_t)cfg->nxform * n * 4);
     UP(h->d_send, A->send, (size_t)cfg->nsend);
 
+    // Euler: the column-sweep path (euler_sweep.cu, default) or the two-kernel path of euler3d.cu (WXB_EULER_PATH=split)
+    h->sweep = false;
+    if (euler) {
+        const char* pe = getenv("WXB_EULER_PATH");
+        h->sweep = !(pe && strcmp(pe, "split") == 0);
+    }
     // trace array: local part (SW [ntr][nfaces][E][F], Euler [E][nfaces][ntr][F]), then the ghost records
-    // (SW [rec][ntr][1][F], Euler [rec][nz][ntr][F]); the same number of doubles either way
+    // (SW [rec][ntr][1][F], Euler [rec][nz][ntr][F]); the same number of doubles either way.  The sweep path has no
+    // local traces: only the ghost tail exists, addressed through the same offsets.
     h->trace_local = (int64_t)h->ntr * h->nfaces * h->E * h->F;
     const int64_t ghost = (int64_t)cfg->nghost * h->ntr * nz * h->F;
-    CU(cudaMalloc((void**)&h->d_trace, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
-    CU(cudaMemset(h->d_trace, 0, (size_t)(h->trace_local + ghost + 1) * sizeof(double)));
+    {
+        const int64_t alloc = (h->sweep ? 0 : h->trace_local) + ghost + 1;
+        CU(cudaMalloc((void**)&h->d_trace_alloc, (size_t)alloc * sizeof(double)));
+        CU(cudaMemset(h->d_trace_alloc, 0, (size_t)alloc * sizeof(double)));
+        h->d_trace = h->sweep ? h->d_trace_alloc - h->trace_local : h->d_trace_alloc;
+    }
     if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->ntr * nz * h->F * sizeof(double)));
+    if (h->sweep) {
+        std::vector<double> tab(WXB_FASTTAB_DOUBLES);
+        wxbfm::fill_tables(tab.data());
+        UP(h->d_fasttab, tab.data(), tab.size());
+        // tiles of TJ x TI columns, slab after slab, row-major; a tile is "outer" if one of its columns reads a ghost
+        int tj = 1, ti = 1;
+        wxb_sweep_tile_shape(n, &tj, &ti);
+        std::vector<int> tin, tout;
+        const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
+        int tile = 0;
+        for (int s = 0; s < cfg->nslabs; ++s) {
+            const int ny = st.ny[s];
+            for (int j0 = 0; j0 < ny; j0 += tj)
+                for (int i0 = 0; i0 < nx; i0 += ti, ++tile) {
+                    bool g = false;
+                    for (int j = j0; j < ny && j < j0 + tj; ++j)
+                        for (int i = i0; i < nx && i < i0 + ti; ++i) {
+                            const int c = st.cbase[s] + j * nx + i;
+                            for (int f = 0; f < 4; ++f) g = g || (A->nbr[((size_t)f * h->C + c) * 4] >= ghost_base);
+                        }
+                    (g ? tout : tin).push_back(tile);
+                }
+        }
+        h->nt_all = tile;
+        h->nt_inner = (int)tin.size();
+        h->nt_outer = (int)tout.size();
+        if (cfg->nghost > 0) {
+            UP(h->d_tiles_inner, tin.data(), tin.size());
+            UP(h->d_tiles_outer, tout.data(), tout.size());
+        }
+        if (wxb_sweep_configure(n) != 0) {
+            set_err(h, "cannot configure the sweep kernel's shared memory: %s", cudaGetErrorString(cudaGetLastError()));
+            return WXB_ECUDA;
+        }
+    }
 
     // inner / outer element lists: an element is "outer" if one of its horizontal faces reads a ghost record
-    if (cfg->nghost > 0) {
+    if (cfg->nghost > 0 && !h->sweep) {
         std::vector<int> inner, outer;
         const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
         for (int s = 0; s < cfg->nslabs; ++s) {
@@ -247,7 +294,7 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     for (int r = 0; r < WXB_TIMING_RING; ++r)
         for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev_ring[r][i]));
     h->ev = h->ev_ring[0];
-    if (euler && wxb_euler_configure(n) != 0) {
+    if (euler && !h->sweep && wxb_euler_configure(n) != 0) {
         set_err(h, "cannot configure the main kernel's shared memory: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;
     }
@@ -292,20 +339,17 @@ void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, con
     a.has_damp = h->cfg.has_damping;
     a.has_topo = h->cfg.has_topo;
     a.tau0 = h->cfg.damp_tau0;
-    {
-        static const int dbg = getenv("WXB_KERNEL_OPTS") ? atoi(getenv("WXB_KERNEL_OPTS")) : 0;
-        a.dbg = dbg;
-    }
+    a.fasttab = h->d_fasttab;
+    a.tlist = nullptr;
+    a.ntiles = h->nt_all;
+    a.k0 = 0;
+    a.k1 = a.nz;
     a.st = h->st;
 }
 
 int check_mode(wxb_handle* h, const double* q, const double* v, const double* rhs0, double eps, int mode, double* out) {
     if (!q || !out) {
         set_err(h, "null state/output pointer");
-        return WXB_EINVAL;
-    }
-    if (h->cfg.equations == WXB_EQ_EULER3D && h->n % 2 == 0 && ((uintptr_t)q & 15)) {
-        set_err(h, "state pointer must be 16-byte aligned (element rows are moved with TMA bulk copies)");
         return WXB_EINVAL;
     }
     if (mode != -1 && mode != WXB_JVP_FD && mode != WXB_JVP_RAT) {
@@ -325,15 +369,20 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
         h->traces_done = true;
         return WXB_OK;
     }
-    if (v && !h->d_qp) {  // first JVP on this handle: scratch for the perturbed state
+    if (v && !h->d_qp && !h->sweep) {  // first JVP on this handle: scratch for the perturbed state
         CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     }
     EvalArgs a;
     fill_args(h, a, q, v, nullptr, 0.0, eps, -1, nullptr);
     h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     CU(cudaEventRecord(h->ev[0], s));
-    int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
-    if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, h->cfg.equations == WXB_EQ_EULER3D, s);
+    int r;
+    if (h->sweep) {  // no trace array: only the records other ranks need, straight into the send buffer
+        r = wxb_euler_edge_traces(a, h->n, s);
+    } else {
+        r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
+        if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, h->cfg.equations == WXB_EQ_EULER3D, s);
+    }
     if (r != 0) {
         set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;
@@ -361,6 +410,9 @@ int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs
     if (part == 1 || part == 2) {
         if (h->cfg.nghost == 0) {
             if (part == 2) return WXB_OK;  // everything is inner
+        } else if (h->sweep) {
+            a.tlist = part == 1 ? h->d_tiles_inner : h->d_tiles_outer;
+            a.ntiles = part == 1 ? h->nt_inner : h->nt_outer;
         } else {
             a.elist = part == 1 ? h->d_elist_inner : h->d_elist_outer;
             a.nelist = part == 1 ? h->n_inner : h->n_outer;
@@ -369,7 +421,8 @@ int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs
         set_err(h, "part must be 0, 1 or 2");
         return WXB_EINVAL;
     }
-    int r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_main(a, h->n, s) : wxb_sw_main(a, h->n, s);
+    int r = h->sweep ? wxb_euler_sweep(a, h->n, s)
+                     : (h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_main(a, h->n, s) : wxb_sw_main(a, h->n, s));
     if (r != 0) {
         set_err(h, "main kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;
@@ -447,7 +500,7 @@ int wxb_destroy(wxb_handle* h) {
     if (h->d_metric) h->d_sqrtg = h->d_h = h->d_chris = h->d_idz = nullptr;  // views into d_metric
     void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
-                    h->d_elist_inner,      h->d_elist_outer, h->d_trace, h->d_sendbuf, h->d_qp,  h->d_q,           h->d_v,
+                    h->d_elist_inner,      h->d_elist_outer, h->d_trace_alloc, h->d_sendbuf, h->d_fasttab, h->d_tiles_inner, h->d_tiles_outer, h->d_qp,  h->d_q,           h->d_v,
                     h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist, h->d_expf};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -615,7 +668,7 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     const bool jvp = mode >= 0;
     int r = check_mode(h, d_q, jvp ? d_v : nullptr, jvp ? d_r0 : nullptr, eps, mode, d_out);
     if (r != WXB_OK) return r;
-    if (jvp && !h->d_qp) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
+    if (jvp && !h->d_qp && !h->sweep) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     const int nc = h->nchunk;
     // uploads, chunk by chunk
     for (int c = 0; c < nc; ++c) {
@@ -631,6 +684,7 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     cudaStream_t sc = h->s_cmp;
     CU(cudaEventRecord(h->ev[0], sc));
     auto traces = [&](int c) -> int {
+        if (h->sweep) return 0;  // the sweep kernel extrapolates from the state itself
         if (nc > 1) {
             at.elist = h->d_clist + h->chunk_off[c];
             at.nelist = h->chunk_off[c + 1] - h->chunk_off[c];
@@ -638,6 +692,11 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
         return euler ? wxb_euler_traces(at, h->n, sc) : wxb_sw_traces(at, h->n, sc);
     };
     auto maink = [&](int c) -> int {
+        if (h->sweep) {  // levels of chunk c; the levels either side of it have been uploaded (see the loop below)
+            am.k0 = h->chunk_k[c];
+            am.k1 = h->chunk_k[c + 1];
+            return wxb_euler_sweep(am, h->n, sc);
+        }
         if (nc > 1) {
             am.elist = h->d_clist + h->chunk_off[c];
             am.nelist = h->chunk_off[c + 1] - h->chunk_off[c];

@@ -57,10 +57,13 @@ struct EvalArgs {
     const double* ops;    // ext_w[n] ext_e[n] diff[n*n] corr[2n] hfilt[n*n] (Euler: + dlogp[n*n] klogp[n], wxb_api.cu)
     const int* elist;     // optional list of elements to process (nullptr = all)
     int nelist;
+    // column-sweep path (euler_sweep.cu)
+    const double* fasttab;  // log / exp tables (fastmath.cuh)
+    const int* tlist;       // optional list of tiles to process (nullptr = all)
+    int ntiles;             // blocks to launch
+    int k0, k1;             // levels [k0, k1) to sweep
     int E, C, nz, nx, nsend;
     int has_damp, has_topo;
-    int dbg;              // WXB_KERNEL_OPTS bit mask: 4 = TMA-staged variant of euler_main (even n); 1 / 2 = skip the
-                          // interface / node phase (timing experiments only, results are wrong)
     double tau0;
     SlabTab st;
 };
@@ -80,6 +83,12 @@ struct wxb_handle {
     int4* d_nbr;
     int *d_send, *d_elist_inner, *d_elist_outer;
     int n_inner, n_outer;
+    // column-sweep path of the Euler equations (euler_sweep.cu): one launch per evaluation, no local trace array
+    bool sweep;
+    double* d_fasttab;
+    double* d_trace_alloc;   // what was really allocated for d_trace (sweep: the ghost records only)
+    int *d_tiles_inner, *d_tiles_outer;
+    int nt_all, nt_inner, nt_outer;
     double *d_trace, *d_sendbuf, *d_qp;
     int64_t trace_local;  // doubles in the local part of the trace array
     // staging for the *_host entry points
@@ -109,6 +118,10 @@ struct wxb_handle {
 int wxb_euler_configure(int n);
 int wxb_euler_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_main(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_sweep_configure(int n);
+void wxb_sweep_tile_shape(int n, int* tj, int* ti);
+int wxb_euler_sweep(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_euler_edge_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_main(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_pack(const EvalArgs& a, int ntr, int F, int nfaces, int elem_major, cudaStream_t s);

@@ -21,6 +21,7 @@ torch CUDA tensor out (device-resident path).  complex128 input (the reference's
 
 import ctypes
 import math
+import os
 
 import numpy
 
@@ -54,6 +55,9 @@ class RhsB200:
         self.group = process_group
         euler = problem.equations == "euler"
         self.num_var = problem.num_var
+        # Euler: the fused column-sweep kernel (csrc/euler_sweep.cu, default) or the traces + main pair of
+        # csrc/euler3d.cu (WXB_EULER_PATH=split); read by wxb_create
+        self.sweep = euler and os.environ.get("WXB_EULER_PATH", "sweep") != "split"
         # trace fields per face point: the Euler kernels carry 6 (csrc/euler3d.cu, WXB_TRACE_FIELDS)
         self.num_trace = 6 if euler else 3
         nz = problem.nz if euler else 1
@@ -136,6 +140,8 @@ class RhsB200:
         adv = self.prob.equations == "euler" and self.prob.advection_only
         if adv:
             return 0
+        if self.sweep:  # one sweep launch (two on a multi-rank handle: inner, outer tiles) + the edge-trace kernel
+            return 1 + (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
         return 2 + (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
 
     def _tm(self):

@@ -100,12 +100,27 @@ def write_restart(rhs, local, config_content, output_dir, step_id, dt, group=Non
 
 
 def read_restart(rhs, input_file_name, group=None):
-    """OutputManager.load_state_from_file (output_manager.py:97-124): the local state of this rank + the INI text."""
-    state = content = None
+    """OutputManager.load_state_from_file (output_manager.py:97-124): the local state of this rank + the INI text.
+    Rank 0 reads the file; a missing / corrupt file or a state of the wrong shape raises on EVERY rank (the reference
+    raises on every rank after distributing the state), never on rank 0 alone while the others wait in a collective."""
+    state = content = error = None
     if rhs.rank == 0:
-        state, _, content = load_state(input_file_name)
-        if tuple(state.shape) != tuple(rhs.prob.state_shape):
-            raise ValueError(f"ERROR reading state vector from file. The shape is wrong! ({state.shape}, should be {rhs.prob.state_shape})")
+        try:
+            state, _, content = load_state(input_file_name)
+            if tuple(state.shape) != tuple(rhs.prob.state_shape):
+                raise ValueError(f"ERROR reading state vector from file. The shape is wrong! ({state.shape}, should be {rhs.prob.state_shape})")
+        except Exception as e:  # noqa: BLE001 -- shipped to the other ranks below
+            state, error = None, e
+    if rhs.nranks > 1:
+        import torch.distributed as dist
+
+        box = [(type(error).__name__, str(error)) if error is not None else None, content]
+        dist.broadcast_object_list(box, src=0, group=group)
+        if box[0] is not None and error is None:
+            error = (ValueError if box[0][0] == "ValueError" else OSError)(box[0][1])
+        content = box[1]
+    if error is not None:
+        raise error
     return scatter_state(rhs, state, group), content
 
 

@@ -84,13 +84,20 @@ class VecOps:
         W: 2-D tensor (>= k rows, N) or 1-D (k = 1)."""
         n = V.shape[-1]
         ldw = W.stride(0) if W.dim() == 2 else n
+        ldv = V.stride(0) if V.dim() == 2 else n
+        if m * k > self._small.numel():  # PMEX reaches mmax + 1 rows (wx_factory/solvers/pmex.py:150-230)
+            self._small = self.torch.empty(2 * m * k, dtype=self.torch.float64, device=self.device)
         out = self._small[: m * k]
-        self._chk(
-            self.lib.wxb_vec_multidot(n, m, V.data_ptr(), V.stride(0) if V.dim() == 2 else n, k, W.data_ptr(), ldw, out.data_ptr(),
-                                      self._scratch.data_ptr(), _sp(self.torch, self.device)),
-            "wxb_vec_multidot",
-        )
-        self.launches += (m + 7) // 8 + 1  # MD_ROWS rows per pass + the final reduction (csrc/stepops.cu)
+        # the kernel takes up to WXB_VEC_MAX_ROWS rows per call: longer bases go in chunks of rows, each chunk's
+        # (rows x k) block landing at its place in `out`
+        for r0 in range(0, m, self.max_rows):
+            mr = min(self.max_rows, m - r0)
+            self._chk(
+                self.lib.wxb_vec_multidot(n, mr, V.data_ptr() + 8 * r0 * ldv, ldv, k, W.data_ptr(), ldw, out[r0 * k :].data_ptr(),
+                                          self._scratch.data_ptr(), _sp(self.torch, self.device)),
+                "wxb_vec_multidot",
+            )
+            self.launches += (mr + 7) // 8 + 1  # MD_ROWS rows per pass + the final reduction (csrc/stepops.cu)
         if self.world_size > 1:
             import torch.distributed as dist
 
