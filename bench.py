@@ -8,15 +8,22 @@
 Metric (BASELINE.json): FP64 DOF-updates/s.  One *step* = one RHS evaluation dQ/dt = RHS(Q) followed by one fused
 finite-difference Jacobian-vector product J(Q) v around it (what an EPI/KIOPS or Rosenbrock/FGMRES integrator does per
 Krylov vector), i.e. 2 x (5 x nodes) DOF-updates.  Workload = BASELINE.json configs[4], the synthetic
-high-resolution Euler state (n = 4, 12 x nh x nh elements per panel, nh = 48 at one GPU and ~48*sqrt(N) at N so
-that the elements per GPU stay fixed: weak scaling): metric, operators and state of a reference-built DCMIP 3-1
-problem tiled along the element axes (wxfactory_b200/synthetic.py).  The four .ini configs of BASELINE.json hold
-16 k .. 146 k DOFs -- microseconds of HBM time, launch-bound -- and are parity-test cases, not bench lines.
+high-resolution Euler state at the largest single-GPU size of SURVEY.md section 8(d), S2 s = 1: n = 4, 24 x 96 x 96
+elements per panel (85 M nodes, 425 M DOFs, ~30 GB resident) at one GPU and nh ~ 96*sqrt(N) at N so that the elements per
+GPU stay fixed (weak scaling; s = 2 at N = 8): metric, operators and state of a reference-built DCMIP 3-1 problem tiled
+along the element axes (wxfactory_b200/synthetic.py).  The four .ini configs of BASELINE.json hold 16 k .. 146 k DOFs --
+microseconds of HBM time, launch-bound -- and are parity-test cases, not bench lines.
+
+Protocol: W warm-up steps, then --repeats (5) timed loops of exactly K steps each, every loop bracketed by
+barrier + synchronize and timed with CUDA events, max over ranks; `value` / `ms_per_step` are the MEDIAN loop.  A further
+back-to-back loop of >= 2 s gives the `sustained` object (clocks sampled separately).  `sweep` holds the smaller S2 sizes
+(s = 1/4, 1/2) at N = 1; `strong` (N > 1) the fixed s = 1 problem cut N ways in the same run.
 
 JSON line keys (one line, rank 0): the base contract's, plus
   roofline      algorithmic HBM bytes of one RHS evaluation (B_rhs(n) = 360 + 96/n bytes per node) over the
-                evaluation's device time (both kernels of the evaluation: traces + main), measured with the C
-                ABI's own CUDA events on the launching stream for every RHS launch of the timed region;
+                evaluation's device time (the sweep kernel, or traces + main on the split path), measured with the C
+                ABI's own CUDA events on the launching stream for every RHS launch of the timed loops (median = burst
+                figure; `sustained` = mean over the last evaluations of the >= 2 s loop);
                 roofline_jvp is the same for the JVP launches (B_jvp(n) = 440 + 96/n).
   e2e           the same step through the public API with HOST numpy arrays (pinned): H2D of every input and D2H
                 of every result inside the timed region.
@@ -65,12 +72,36 @@ def b_jvp(n):
     return 440.0 + 96.0 / n  # + v and the cached base RHS
 
 
-# DRAM bytes per node and evaluation actually moved by the two kernels (dram__bytes_read.sum + dram__bytes_write.sum
-# of euler_traces + euler_main, n = 4), from the `ncu --set full` capture at the bench's own size summarised in
-# profiles/r01_final3_ncu.txt (12x48x48 elements/panel, 10 616 832 nodes).  Re-measure when the kernels change.
-NCU_TRAFFIC_NODES = 10616832
-NCU_TRAFFIC_PER_NODE = {"rhs": (0.424689e9 + 0.706788e9 + 4.501844e9 + 0.420585e9) / NCU_TRAFFIC_NODES,
-                        "jvp": (0.849363e9 + 1.133382e9 + 4.966819e9 + 0.419694e9) / NCU_TRAFFIC_NODES}
+# DRAM bytes per node and evaluation actually moved by the Euler kernels (dram__bytes_read.sum + dram__bytes_write.sum,
+# n = 4) come from an `ncu --set full` capture summarised under profiles/ and recorded in profiles/ncu_traffic.json
+# together with a hash of the kernel sources (scripts/ncu_traffic.py).  A capture made from other sources is stale: the
+# line then says "traffic": null.
+KERNEL_SOURCES = ["euler_sweep.cu", "euler3d.cu", "fastmath.cuh", "wxb_internal.cuh"]
+
+
+def kernel_source_hash():
+    import hashlib
+
+    h = hashlib.sha256()
+    for f in KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "wxfactory_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(path_name):
+    """(bytes per node {rhs, jvp}, source note) for the Euler path in use, or (None, why)."""
+    fn = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(fn):
+        return None, "no profiles/ncu_traffic.json"
+    with open(fn) as f:
+        rec = json.load(f)
+    ent = rec.get(path_name)
+    if not ent:
+        return None, f"no capture of the {path_name} path"
+    if ent.get("source_hash") != kernel_source_hash():
+        return None, f"stale: {ent.get('report')} was captured from other kernel sources"
+    return {"rhs": ent["rhs_bytes"] / ent["nodes"], "jvp": ent["jvp_bytes"] / ent["nodes"]}, ent.get("report")
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -226,12 +257,56 @@ def measured_peaks():
 
 
 # ------------------------------------------------------------------------------------------------------------
+def _median(xs):
+    return float(statistics.median(xs))
+
+
+class Workload:
+    """One tiled Euler problem on this rank: handle, device-resident and pinned host copies of the state / direction."""
+
+    def __init__(self, base, ex, nz, nh, world, rank, local_rank, host=True):
+        import torch
+
+        from wxfactory_b200 import RhsB200
+        from wxfactory_b200 import synthetic as syn
+
+        self.nz, self.nh = nz, nh
+        self.tiled = syn.TiledEulerProblem(base, nz, nh)
+        t0 = time.perf_counter()
+        self.rhs = RhsB200(self.tiled, nranks=world, rank=rank, device=local_rank)
+        self.size = self.rhs.size
+        self.nodes_local = self.size // 5
+        Qb = syn.base_state(ex["Q0"])
+        vb = syn.base_direction(Qb)
+        self.Qb, self.vb = Qb, vb
+        dev = torch.device("cuda", local_rank)
+        if host:  # host copies live in pinned memory: they are what the reference's integrators would hold
+            pin = lambda: torch.empty(self.size, dtype=torch.float64, pin_memory=True)  # noqa: E731
+            self.q_h, self.v_h = pin(), pin()
+            self.q_h.numpy()[:] = self.rhs.local_state(Qb)
+            self.v_h.numpy()[:] = self.rhs.local_state(vb)
+            self.q_d, self.v_d = self.q_h.to(dev), self.v_h.to(dev)
+        else:
+            self.q_d = torch.from_numpy(self.rhs.local_state(Qb)).to(dev)
+            self.v_d = torch.from_numpy(self.rhs.local_state(vb)).to(dev)
+        self.dt = float(ex["dt"])
+        self.setup_s = time.perf_counter() - t0
+
+    def step_device(self):
+        out = self.rhs(self.q_d)
+        return self.rhs.jvp(self.v_d, self.dt, self.q_d, out, mode="fd")
+
+    def close(self):
+        self.rhs.close()
+        self.q_d = self.v_d = self.q_h = self.v_h = None
+
+
 def run_b200(args):
     import numpy
     import torch
     import torch.distributed as dist
 
-    from wxfactory_b200 import EPS_FD, RhsB200
+    from wxfactory_b200 import EPS_FD
     from wxfactory_b200 import synthetic as syn
     from wxfactory_b200.problem import load_problem
 
@@ -259,65 +334,71 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def timed_loop(fn, steps):
+        """Exactly `steps` calls between two CUDA events, barrier + synchronize on both sides; ms, max over ranks."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        w0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), (w0 - 0.05, time.perf_counter() + 0.05)
+
     # ---- workload -----------------------------------------------------------------------------------------
     base, ex = load_problem(BASE_FIXTURE)
     n = base.n
     nz = args.nz
     nh = args.nh if args.nh > 0 else nh_for(world, args.nh1)
-    tiled = syn.TiledEulerProblem(base, nz, nh)
-    Qb = syn.base_state(ex["Q0"])
-    vb = syn.base_direction(Qb)
-    dt = float(ex["dt"])
-    t_setup = time.perf_counter()
-    rhs = RhsB200(tiled, nranks=world, rank=rank, device=local_rank)
-    size = rhs.size
-    nodes_local = size // 5
-    # host copies live in pinned memory: they are what the reference's integrators would hold
-    pin = lambda: torch.empty(size, dtype=torch.float64, pin_memory=True)  # noqa: E731
-    q_h, v_h, r0_h = pin(), pin(), pin()
-    q_h.numpy()[:] = rhs.local_state(Qb)
-    v_h.numpy()[:] = rhs.local_state(vb)
-    q_d, v_d = q_h.to(dev), v_h.to(dev)
-    t_setup = time.perf_counter() - t_setup
+    wl = Workload(base, ex, nz, nh, world, rank, local_rank)
+    rhs, tiled, size, nodes_local, dt = wl.rhs, wl.tiled, wl.size, wl.nodes_local, wl.dt
+    q_d, v_d, q_h, v_h = wl.q_d, wl.v_d, wl.q_h, wl.v_h
+    r0_h = torch.empty(size, dtype=torch.float64, pin_memory=True)
     total_nodes = tiled.num_nodes
     total_dofs = tiled.num_dofs
     state_bytes = size * 8
+    path_name = "sweep" if rhs.sweep else "split"
 
     # ---- full-size parity through the tiling periodicity property (untimed) ---------------------------------
-    parity = None
-    rhs0_d = rhs(q_d)
-    jv_d = rhs.jvp(v_d, dt, q_d, rhs0_d, mode="fd")
-    torch.cuda.synchronize()
-    if not args.skip_check:
+    small_ref = None
+
+    def parity_of(w):
+        """rhs / jvp of workload w against the oracle on the 8x8x8 twin, over every comparable element."""
+        nonlocal small_ref
         from oracle import jvp_oracle
 
-        small = syn.TiledEulerProblem(base, SMALL_NZ, SMALL_NH)
-        orc = jvp_oracle.make_oracle(small.materialize())
-        Qs, vs = small.global_state(Qb), small.global_state(vb)
-        with numpy.errstate(all="ignore"):
-            want_r = orc.rhs(Qs)
-            want_j = jvp_oracle.matvec_fd(orc.rhs, vs.ravel(), dt, Qs, want_r).reshape(Qs.shape)
-        e_r, cnt = syn.check_against_small(tiled, rhs.part, rhs0_d, want_r)
-        e_j, _ = syn.check_against_small(tiled, rhs.part, jv_d, want_j)
+        if small_ref is None:
+            small = syn.TiledEulerProblem(base, SMALL_NZ, SMALL_NH)
+            orc = jvp_oracle.make_oracle(small.materialize())
+            Qs, vs = small.global_state(w.Qb), small.global_state(w.vb)
+            with numpy.errstate(all="ignore"):
+                want_r = orc.rhs(Qs)
+                want_j = jvp_oracle.matvec_fd(orc.rhs, vs.ravel(), w.dt, Qs, want_r).reshape(Qs.shape)
+            small_ref = (want_r, want_j)
+        want_r, want_j = small_ref
+        r = w.rhs(w.q_d)
+        j = w.rhs.jvp(w.v_d, w.dt, w.q_d, r, mode="fd")
+        torch.cuda.synchronize()
+        e_r, cnt = syn.check_against_small(w.tiled, w.rhs.part, r, want_r)
+        e_j, _ = syn.check_against_small(w.tiled, w.rhs.part, j, want_j)
         # the FD formula amplifies RHS rounding by dt/eps: state the JVP error relative to dt*|rhs|/eps
-        jscale = dt * float(numpy.linalg.norm(want_r)) / EPS_FD / max(float(numpy.linalg.norm(want_j)), 1e-300)
-        e_j_scaled = e_j / jscale
-        e_r, e_j_scaled, cnt = max_over_ranks(e_r), max_over_ranks(e_j_scaled), int(max_over_ranks(float(cnt)))
-        parity = {
+        jscale = w.dt * float(numpy.linalg.norm(want_r)) / EPS_FD / max(float(numpy.linalg.norm(want_j)), 1e-300)
+        e_r, e_j, cnt = max_over_ranks(e_r), max_over_ranks(e_j / jscale), int(max_over_ranks(float(cnt)))
+        return {
             "rhs_rel_err": e_r,
-            "jvp_err_over_dt_rhs_eps": e_j_scaled,
+            "jvp_err_over_dt_rhs_eps": e_j,
             "elements_checked_per_rank": cnt,
             "tolerance": 1e-12,
-            "ok": bool(e_r <= 1e-12 and e_j_scaled <= 1e-12),
+            "ok": bool(e_r <= 1e-12 and e_j <= 1e-12),
+            "ranks": world,
             "how": "every element off the panel edges / bottom / top vs the numpy oracle on the 8x8x8 twin (tiling periodicity)",
         }
-        del orc, Qs, vs, want_r, want_j
+
+    parity = None if args.skip_check else parity_of(wl)
+    rhs0_d = rhs(q_d)
     r0_h.copy_(rhs0_d)
     torch.cuda.synchronize()
-
-    def step_device():
-        out = rhs(q_d)
-        return rhs.jvp(v_d, dt, q_d, out, mode="fd")
 
     def step_host():
         if world > 1:  # multi-rank handles: numpy in / out through the device path (H2D, halo exchange, D2H)
@@ -331,68 +412,80 @@ def run_b200(args):
         sampler.start()
         time.sleep(0.3)
 
-    # ---- device-resident timed region -----------------------------------------------------------------------
+    # ---- device-resident timed loops: --repeats loops of exactly --steps steps, the median loop is the headline ------
     for _ in range(args.warmup):
-        step_device()
-    barrier()
+        wl.step_device()
     launches0 = rhs.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    w0 = time.perf_counter()
-    e0.record()
-    for _ in range(args.steps):
-        step_device()
-    e1.record()
-    barrier()
-    w1 = time.perf_counter()
-    launches = rhs.launches - launches0
-    ms_dev = max_over_ranks(e0.elapsed_time(e1))
-    hist, modes = rhs.timing_history(min(256, 2 * args.steps))
-    t_rhs = hist[modes < 0]
-    t_jvp = hist[modes >= 0]
+    loop_ms, loop_windows, t_rhs, t_jvp = [], [], [], []
+    for _ in range(args.repeats):
+        ms, win = timed_loop(wl.step_device, args.steps)
+        loop_ms.append(ms)
+        loop_windows.append(win)
+        hist, modes = rhs.timing_history(min(256, 2 * args.steps))
+        t_rhs.append(hist[modes < 0])
+        t_jvp.append(hist[modes >= 0])
+    launches = (rhs.launches - launches0) // args.repeats
+    ms_dev = _median(loop_ms)
+    t_rhs, t_jvp = numpy.concatenate(t_rhs), numpy.concatenate(t_jvp)
+
+    # ---- sustained: one back-to-back loop of >= --sustain-s seconds ---------------------------------------------------
+    sustained = None
+    sus_win = None
+    if args.sustain_s > 0:
+        sus_steps = max(args.steps, int(math.ceil(args.sustain_s * 1e3 / (ms_dev / args.steps))))
+        ms_sus, sus_win = timed_loop(wl.step_device, sus_steps)
+        hist, modes = rhs.timing_history(256)
+        sustained = {"steps": sus_steps, "seconds": ms_sus * 1e-3, "ms_per_step": ms_sus / sus_steps,
+                     "value": 2.0 * total_dofs * sus_steps / (ms_sus * 1e-3), "unit": UNIT,
+                     "_rhs_ms": float(hist[modes < 0][:, 2].mean()), "_jvp_ms": float(hist[modes >= 0][:, 2].mean())}
 
     # ---- end to end through the public API with host arrays ------------------------------------------------
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
     for _ in range(2):
         step_host()
-    barrier()
-    w2 = time.perf_counter()
-    e0.record()
-    for _ in range(e2e_steps):
-        step_host()
-    e1.record()
-    barrier()
-    w3 = time.perf_counter()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    ms_e2e, e2e_win = timed_loop(step_host, e2e_steps)
     if sampler:
         time.sleep(0.2)
         sampler.stop()
 
     peak, peak_src = measured_peaks()
+    traffic, traffic_src = ncu_traffic(path_name) if n == 4 else (None, "captured at n = 4 only")
+    kernels = ["euler_sweep<4>"] if rhs.sweep else ["euler_traces<4>", "euler_main<4>"]
     line = None
     if rank == 0:
-        def roof(tt, bytes_per_node, what, key):
+        def roof(tt, bytes_per_node, what, key, sus_ms):
             if len(tt) == 0:
                 return None
-            sec = float(tt[:, 2].mean()) * 1e-3
-            ach = bytes_per_node * nodes_local / sec / 1e9
-            return {
+            ev_ms = _median(tt[:, 2])
+            ach = bytes_per_node * nodes_local / (ev_ms * 1e-3) / 1e9
+            out = {
                 "bound": "hbm",
                 "achieved": ach,
                 "peak": peak,
                 "unit": "GB/s",
                 "frac": ach / peak,
-                "traffic": NCU_TRAFFIC_PER_NODE[key] * nodes_local if n == 4 else None,
-                "traffic_source": "profiles/r01_final3_ncu.txt (ncu DRAM bytes per node at 10.6 M nodes x this launch's nodes)",
-                "kernels": ["euler_traces<4>", "euler_main<4>"],
-                "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
+                "traffic": traffic[key] * nodes_local if traffic else None,
+                "traffic_source": traffic_src,
+                "kernels": kernels,
+                "launch_ms": {"traces": _median(tt[:, 0]), "main": _median(tt[:, 1]), "evaluation": ev_ms},
                 "algorithmic_bytes_per_node": bytes_per_node,
                 "nodes_per_launch": nodes_local,
                 "launches_timed": int(len(tt)),
                 "peak_source": peak_src,
-                "what": what,
+                "what": what + " (burst: median over the launches of the timed loops)",
             }
+            if sus_ms is not None:
+                a2 = bytes_per_node * nodes_local / (sus_ms * 1e-3) / 1e9
+                out["sustained"] = {"achieved": a2, "frac": a2 / peak, "evaluation_ms": sus_ms,
+                                    "what": f"mean over the last evaluations of the {sustained['seconds']:.1f} s back-to-back loop"}
+            return out
 
-        clocks = sampler.summary([(w0 - 0.15, w1 + 0.15), (w2, w3)]) if sampler else None
+        clocks = sampler.summary(loop_windows + [e2e_win]) if sampler else None
+        if sustained is not None:
+            rhs_sus, jvp_sus = sustained.pop("_rhs_ms"), sustained.pop("_jvp_ms")
+            sustained["clocks"] = sampler.summary([sus_win]) if sampler else None
+        else:
+            rhs_sus = jvp_sus = None
         line = {
             "metric": METRIC,
             "value": 2.0 * total_dofs * args.steps / (ms_dev * 1e-3),
@@ -413,8 +506,11 @@ def run_b200(args):
                 "nodes": total_nodes,
                 "dofs": total_dofs,
                 "step": "1 RHS + 1 fused FD-JVP = 2 x dofs DOF-updates",
+                "kernel_path": path_name,
                 "partition": f"{world} rank(s), contiguous rows of element columns; face-trace halo over NCCL p2p",
                 "l2": f"state {state_bytes / 2**20:.0f} MiB + metric {nodes_local * 35 * 8 / 2**20:.0f} MiB per GPU > L2 ({L2_BYTES >> 20} MiB): no flush needed",
+                "protocol": f"{args.repeats} loops of {args.steps} steps, median loop reported; all loops ms: " + ", ".join(f"{m:.3f}" for m in loop_ms),
+                "parity_ok": None if parity is None else parity["ok"],
             },
             "e2e": {
                 "value": 2.0 * total_dofs * e2e_steps / (ms_e2e * 1e-3),
@@ -432,15 +528,59 @@ def run_b200(args):
                 ),
             },
             "gpu_launches": int(launches),
-            "roofline": roof(t_rhs, b_rhs(n), "one RHS evaluation", "rhs"),
-            "roofline_jvp": roof(t_jvp, b_jvp(n), "one fused FD-JVP evaluation (cached base RHS)", "jvp"),
+            "roofline": roof(t_rhs, b_rhs(n), "one RHS evaluation", "rhs", rhs_sus),
+            "roofline_jvp": roof(t_jvp, b_jvp(n), "one fused FD-JVP evaluation (cached base RHS)", "jvp", jvp_sus),
+            "sustained": sustained,
             "clocks": clocks,
             "parity": parity,
-            "setup_s": t_setup,
+            "setup_s": wl.setup_s,
         }
     if world == 1 and line is not None and not args.skip_stepops:
         line["stepops"] = measure_stepops(rhs, q_d, rhs0_d, peak)
-    rhs.close()
+    del rhs0_d, q_d, v_d, q_h, v_h, r0_h
+    wl.close()
+    torch.cuda.empty_cache()
+
+    def quick(nzq, nhq, reps=3):
+        """A second problem size in the same process: parity, then `reps` loops of --steps steps (median)."""
+        w = Workload(base, ex, nzq, nhq, world, rank, local_rank, host=False)
+        par = None if args.skip_check else parity_of(w)
+        for _ in range(args.warmup):
+            w.step_device()
+        ms = []
+        tr, tj = [], []
+        for _ in range(reps):
+            m, _ = timed_loop(w.step_device, args.steps)
+            ms.append(m)
+            hist, modes = w.rhs.timing_history(min(256, 2 * args.steps))
+            tr.append(hist[modes < 0][:, 2])
+            tj.append(hist[modes >= 0][:, 2])
+        m = _median(ms)
+        er, ej = _median(numpy.concatenate(tr)), _median(numpy.concatenate(tj))
+        out = {
+            "elements_per_panel": [nzq, nhq, nhq], "nodes": w.tiled.num_nodes, "dofs": w.tiled.num_dofs,
+            "value": 2.0 * w.tiled.num_dofs * args.steps / (m * 1e-3), "unit": UNIT, "ms_per_step": m / args.steps,
+            "rhs_ms": er, "jvp_ms": ej,
+            "rhs_frac": b_rhs(n) * w.nodes_local / (er * 1e-3) / 1e9 / peak,
+            "jvp_frac": b_jvp(n) * w.nodes_local / (ej * 1e-3) / 1e9 / peak,
+            "parity": par,
+        }
+        w.close()
+        del w
+        torch.cuda.empty_cache()
+        return out
+
+    if world == 1 and not args.skip_sweep:
+        sw = [quick(max(1, nz // 4), max(4, nh // 4)), quick(max(1, nz // 2), max(4, nh // 2))]
+        if line is not None:
+            line["sweep"] = {"what": "SURVEY 8(d) S2 at s = 1/4 and s = 1/2 of the headline size, same protocol (3 loops, median)", "sizes": sw}
+    if world > 1 and not args.skip_strong and (6 * args.nh1) % world == 0:
+        # strong scaling: the fixed N = 1 problem (S2 s = 1) cut `world` ways, same run
+        st = quick(args.nz, args.nh1)
+        if line is not None:
+            st["what"] = (f"strong scaling: the fixed {args.nz}x{args.nh1}x{args.nh1} problem of the N = 1 line split over {world} ranks; "
+                          "efficiency = value / (N x the N = 1 line's value)")
+            line["strong"] = st
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -631,8 +771,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
-    ap.add_argument("--nz", type=int, default=12, help="elements per column")
-    ap.add_argument("--nh1", type=int, default=48, help="elements per panel side at one GPU (scaled by sqrt(N))")
+    ap.add_argument("--nz", type=int, default=24, help="elements per column (SURVEY 8d S2 s = 1: 24)")
+    ap.add_argument("--nh1", type=int, default=96, help="elements per panel side at one GPU (S2 s = 1: 96; scaled by sqrt(N))")
+    ap.add_argument("--repeats", type=int, default=5, help="timed loops of --steps steps; the median loop is reported")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the back-to-back `sustained` loop in seconds (0: skip)")
+    ap.add_argument("--skip-sweep", action="store_true", help="skip the smaller S2 sizes (s = 1/4, 1/2) at N = 1")
+    ap.add_argument("--skip-strong", action="store_true", help="skip the strong-scaling measurement at N > 1")
     ap.add_argument("--nh", type=int, default=0, help="override the elements per panel side")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-steps", type=int, default=10)

@@ -1,12 +1,15 @@
 """Parity of the CUDA path (through the C ABI) with the reference's golden vectors and with the oracle.
 
 Tolerances (FP64, BASELINE.json north_star: 1e-12 relative per RHS evaluation):
-  RHS_TOL  relative L2 error of the whole RHS and of every variable, vs the reference's own output.  Where the
-           reference's own float64 result is further than that from the exactly-rounded evaluation of its formulas
-           (tests/golden/conditioning.json, made by oracle/refharness/conditioning.py with an 80-bit oracle: only
-           the dcmip31_n4/n5/n6 cases, hydrostatic states at rest whose RHS is a 1e-10-relative residue of cancelling
-           terms), the bound is twice the reference's own rounding error: no other summation order can be expected to
-           agree more closely (measured: the CUDA result differs from the reference by 0.3 .. 1.0 of that error).
+  RHS_TOL  = 1e-12: relative L2 error of the WHOLE right-hand side vs the reference's own output, for every golden case
+           except the three ILL_CONDITIONED ones (dcmip31 physics at n = 4, 5, 6: hydrostatic states at rest whose RHS is
+           a 1e-10-relative residue of cancelling terms).  For those the reference's own float64 result is 8e-11 .. 9e-11
+           away from the exactly-rounded evaluation of its formulas (tests/golden/conditioning.json, made by
+           oracle/refharness/conditioning.py with an 80-bit oracle), so the bound there is twice the reference's own
+           rounding error: no other summation order can be expected to agree more closely.
+           Per variable the bound is 10 x RHS_TOL, or twice the reference's own rounding error of that variable where
+           that is larger (a variable that is a small part of the whole, e.g. the momenta of a state at rest, is
+           conditioned worse than the whole).  Every test prints measured / bound.
   JVP_TOL  FD-JVP error relative to dt*|rhs|/eps (the FD formula amplifies RHS rounding by 1/eps ~ 2900,
            SURVEY 7.3), vs the reference's matvec_fun(..., 'fd') / matvec_rat outputs
 """
@@ -27,7 +30,12 @@ with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "co
     CONDITIONING = json.load(_f)["cases"]
 
 
+ILL_CONDITIONED = ("dcmip31_n4", "dcmip31_n5", "dcmip31_n6")
+
+
 def rhs_tol(name):
+    if name not in ILL_CONDITIONED:
+        return RHS_TOL
     # two independent roundings of the same ill-conditioned quantity differ by up to the sum of their errors
     return max(RHS_TOL, 2 * CONDITIONING[name]["ref_rounding"])
 
@@ -64,7 +72,10 @@ def test_rhs_matches_reference_host_path(rhs_cache, name):
     rhs, prob, ex = rhs_cache(name)
     out = rhs(ex["Q0"])
     assert isinstance(out, numpy.ndarray) and out.shape == ex["Q0"].shape
-    assert rel(out, ex["rhs0"]) <= rhs_tol(name)
+    err = rel(out, ex["rhs0"])
+    print(f"{name}: rhs error {err:.2e} / bound {rhs_tol(name):.2e}; per variable "
+          + " ".join(f"{rel(out[:, v], ex['rhs0'][:, v]):.1e}/{var_tol(name, v):.1e}" for v in range(prob.num_var)))
+    assert err <= rhs_tol(name)
     for v in range(prob.num_var):
         assert rel(out[:, v], ex["rhs0"][:, v]) <= var_tol(name, v), f"variable {v}"
 
@@ -102,9 +113,11 @@ def test_jvp_matches_reference(rhs_cache, name):
     assert numpy.linalg.norm(fd_d.cpu().numpy() - ex["jv_fd"].ravel()) <= JVP_TOL * scale
 
 
-@pytest.mark.parametrize("name", ["dcmip21", "case6"])
+@pytest.mark.parametrize("name", ["dcmip21", "case6", "dcmip31", "galewsky", "case5", "dcmip31_n4", "dcmip21_n5"])
 def test_perturbed_states_match_oracle(rhs_cache, name):
-    """Seeded random perturbations of the golden state, CUDA vs oracle (not only the analytic initial state)."""
+    """Seeded random perturbations of the golden state, CUDA vs oracle (not only the analytic initial state): both
+    Euler orders of the shipped configs, an n = 4 and an n = 5 case, shallow water with and without topography.  A
+    perturbed state is well conditioned (no hydrostatic cancellation): 1e-12 everywhere, dcmip31_n4 included."""
     from oracle import jvp_oracle
 
     rhs, prob, ex = rhs_cache(name)
@@ -114,7 +127,70 @@ def test_perturbed_states_match_oracle(rhs_cache, name):
         Q = ex["Q0"] * (1.0 + 1e-3 * rng.standard_normal(ex["Q0"].shape)) + 1e-6 * rng.standard_normal(ex["Q0"].shape)
         with numpy.errstate(all="ignore"):
             want = orc.rhs(Q)
-        assert rel(rhs(Q), want) <= RHS_TOL
+        err = rel(rhs(Q), want)
+        print(f"{name}: perturbed-state rhs error {err:.2e} / bound {RHS_TOL:.0e}")
+        assert err <= RHS_TOL
+
+
+def test_advection_only_short_cut(golden):
+    """Euler cases < 13 are pure advection: the reference zeroes all five rows of the right-hand side
+    (wx_factory/rhs/rhs_dfr.py:307-313), so RHS == 0, the FD product is 0 and the rational one returns v.  (The shipped
+    configs of that kind, config/dcmip11.ini / dcmip12.ini, crash inside the reference's own RHS -- its 3-D state meets
+    2-D operators -- so there is no golden vector; the branch is checked against its definition.)"""
+    import dataclasses
+
+    import torch
+
+    from wxfactory_b200 import RhsB200, matvec_fun, matvec_rat
+
+    prob, ex = golden("dcmip21")
+    adv = dataclasses.replace(prob, advection_only=True, case_number=11)
+    rhs = RhsB200(adv)
+    try:
+        out = rhs(ex["Q0"])
+        assert out.shape == ex["Q0"].shape and not out.any()
+        q = torch.from_numpy(ex["Q0"]).cuda()
+        outd = rhs(q)
+        assert outd.is_cuda and not bool(outd.any())
+        dt = float(ex["dt"])
+        v = ex["v"].ravel()
+        assert not matvec_fun(v, dt, ex["Q0"], out, rhs, "fd").any()
+        assert numpy.array_equal(matvec_rat(v, dt, ex["Q0"], out, rhs), v)
+        vd = torch.from_numpy(ex["v"]).cuda()
+        assert torch.equal(rhs.jvp(vd, dt, q, outd, mode="rat"), vd.view(-1))
+        assert rhs.launches == 0  # no kernel is needed for it
+    finally:
+        rhs.close()
+
+
+def test_restart_round_trip_with_a_live_handle(golden, tmp_path):
+    """state_io.write_restart / read_restart driven by a live RhsB200 (wx_factory/output/state.py:9-33,
+    wx_factory/output/output_manager.py:97-143): the file read back is the reference-written golden state, the state
+    written from the device-resident solution is byte-identical to the reference's file, and an evaluation from the
+    restarted state equals one from the original."""
+    import glob
+
+    import torch
+
+    from conftest import GOLDEN
+    from wxfactory_b200 import RhsB200, state_io
+
+    prob, ex = golden("dcmip21")
+    ref_file = glob.glob(os.path.join(GOLDEN, "state_dcmip21", "state_vector_*.npy"))[0]
+    rhs = RhsB200(prob)
+    try:
+        local, content = state_io.read_restart(rhs, ref_file)
+        assert numpy.array_equal(local, rhs.local_state(ex["Q0"]))
+        q = torch.from_numpy(local).cuda()
+        r0 = rhs(q)
+        assert rel(r0.cpu().numpy().reshape(ex["rhs0"].shape), ex["rhs0"]) <= RHS_TOL
+        name = state_io.write_restart(rhs, q, content, str(tmp_path), 7, 25.0)  # device tensor in
+        assert os.path.basename(name) == os.path.basename(ref_file)
+        assert open(name, "rb").read() == open(ref_file, "rb").read()
+        again, _ = state_io.read_restart(rhs, name)
+        assert torch.equal(rhs(torch.from_numpy(again).cuda()), r0)
+    finally:
+        rhs.close()
 
 
 def test_complex_state_is_rejected(rhs_cache):

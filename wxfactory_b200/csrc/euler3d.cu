@@ -22,6 +22,7 @@
 // Local point orders (wx_factory/geometry/cubed_sphere_3d.py:764-775):
 //   node = k*n^2 + j*n + i ; x1-face pt = k*n + j ; x2-face pt = k*n + i ; x3-face pt = j*n + i
 //   faces: 0 W(x1-) 1 E(x1+) 2 S(x2-) 3 N(x2+) 4 D(x3-) 5 U(x3+)
+#include "fastmath.cuh"
 #include "wxb_internal.cuh"
 
 // tuning knobs per order n: elements per block (EB) and resident blocks per SM the main kernel is compiled for (MINB);
@@ -64,6 +65,9 @@
 #endif
 #ifndef WXB_RCP
 #define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
+#endif
+#ifndef WXB_FASTMATH
+#define WXB_FASTMATH 1  // table-driven branch-free exp / log / reciprocal / sqrt of fastmath.cuh (tables read through L1)
 #endif
 
 // Formulation knobs of the trace / interface path (A/B'd on B200: profiles/r01_trace_variants.log):
@@ -109,29 +113,38 @@
 
 namespace {
 
+// exp / log / 1/x / sqrt: fastmath.cuh versions (tab = EvalArgs::fasttab in global memory, 4.6 KB that stay in L1) or
+// the CUDA library ones
+__device__ __forceinline__ double m_exp(double x, const double* __restrict__ tab) {
+    return WXB_FASTMATH ? wxbfm::fast_exp(x, tab + WXB_EXPTAB_OFF) : exp(x);
+}
+__device__ __forceinline__ double m_log(double x, const double* __restrict__ tab) { return WXB_FASTMATH ? wxbfm::fast_log(x, tab) : log(x); }
+__device__ __forceinline__ double m_rcp(double x) { return WXB_FASTMATH ? wxbfm::fast_rcp(x) : 1.0 / x; }
+__device__ __forceinline__ double m_sqrt(double x) { return WXB_FASTMATH ? wxbfm::fast_sqrt(x) : sqrt(x); }
+
 constexpr int NVAR = 5;
 constexpr int NTR = 6;                      // trace fields per face point (WXB_TRACE_FIELDS)
 constexpr int NFF = WXB_FOLD_LOGP ? 6 : 7;  // interface results per face point kept for the lift
 
 // extrapolated line sums -> the trace fields (l0 = log rho, l4 = log(rho theta), m1..m3 = momenta)
-__device__ __forceinline__ void trace_fields(double m1, double m2, double m3, double l0, double l4, double out[NTR]) {
-    const double rho = exp(l0);
+__device__ __forceinline__ void trace_fields(double m1, double m2, double m3, double l0, double l4, const double* __restrict__ tab, double out[NTR]) {
+    const double rho = m_exp(l0, tab);
     out[0] = rho;
-    out[4] = exp(l4);
+    out[4] = m_exp(l4, tab);
 #if WXB_TRACE_FIELDS == 1
-    const double r = 1.0 / rho;
+    const double r = m_rcp(rho);
     out[1] = m1 * r;
     out[2] = m2 * r;
     out[3] = m3 * r;
     // a = sqrt(gamma p / rho) with p = p0*exp(gamma*log(Rd/p0 * rho_theta)) (pde_euler_cubesphere.py:158-160,
     // fluxes.py:171-172) from the extrapolated logs with one exp and no sqrt: sqrt(gamma p0) exp((gamma(l4+c) - l0)/2)
-    out[5] = WXB_SQRT_GAMMA_P0 * exp(0.5 * (WXB_GAMMA * (l4 + WXB_LOG_RD_P0) - l0));
+    out[5] = WXB_SQRT_GAMMA_P0 * m_exp(0.5 * (WXB_GAMMA * (l4 + WXB_LOG_RD_P0) - l0), tab);
 #else
     out[1] = m1;
     out[2] = m2;
     out[3] = m3;
 #if WXB_TRACE_FIELDS == 2
-    out[5] = WXB_P0 * exp(WXB_GAMMA * (l4 + WXB_LOG_RD_P0));  // pde_euler_cubesphere.py:158-160 from the extrapolated log
+    out[5] = WXB_P0 * m_exp(WXB_GAMMA * (l4 + WXB_LOG_RD_P0), tab);  // pde_euler_cubesphere.py:158-160 from the extrapolated log
 #else
     out[5] = l4;
 #endif
@@ -175,7 +188,7 @@ __device__ __forceinline__ int element_of(const EvalArgs& a, int slot) {
 // both call this, so the two sides of an interface see bit-identical values.
 template <int N>
 __device__ __forceinline__ void extrap_line(const double* __restrict__ ext, const double* mom, int mom_rs, const double* lrho,
-                                            const double* lrt, int base, int step, double out[NTR]) {
+                                            const double* lrt, int base, int step, const double* __restrict__ tab, double out[NTR]) {
     double a1 = 0.0, a2 = 0.0, a3 = 0.0, l0 = 0.0, l4 = 0.0;
 #pragma unroll
     for (int m = 0; m < N; ++m) {
@@ -187,13 +200,13 @@ __device__ __forceinline__ void extrap_line(const double* __restrict__ ext, cons
         l0 = fma(w, lrho[o], l0);
         l4 = fma(w, lrt[o], l4);
     }
-    trace_fields(a1, a2, a3, l0, l4, out);
+    trace_fields(a1, a2, a3, l0, l4, tab, out);
 }
 
 // both sides of one line at once (shares the loads); per side the same fma chain as extrap_line
 template <int N>
 __device__ __forceinline__ void extrap_line2(const double* __restrict__ ext, const double* mom, int mom_rs, const double* lrho,
-                                             const double* lrt, int base, int step, double lo[NTR], double hi[NTR]) {
+                                             const double* lrt, int base, int step, const double* __restrict__ tab, double lo[NTR], double hi[NTR]) {
     double a[5] = {0, 0, 0, 0, 0}, b[5] = {0, 0, 0, 0, 0};
 #pragma unroll
     for (int m = 0; m < N; ++m) {
@@ -206,8 +219,8 @@ __device__ __forceinline__ void extrap_line2(const double* __restrict__ ext, con
             b[v] = fma(wh, x[v], b[v]);
         }
     }
-    trace_fields(a[0], a[1], a[2], a[3], a[4], lo);
-    trace_fields(b[0], b[1], b[2], b[3], b[4], hi);
+    trace_fields(a[0], a[1], a[2], a[3], a[4], tab, lo);
+    trace_fields(b[0], b[1], b[2], b[3], b[4], tab, hi);
 }
 
 // line of face point pt of direction d: first node and node stride
@@ -258,8 +271,8 @@ euler_traces(const EvalArgs a) {
         s_q[le][0][node] = x[1];
         s_q[le][1][node] = x[2];
         s_q[le][2][node] = x[3];
-        s_q[le][3][node] = log(x[0]);
-        s_q[le][4][node] = log(x[4]);
+        s_q[le][3][node] = m_log(x[0], a.fasttab);
+        s_q[le][4][node] = m_log(x[4], a.fasttab);
     }
     __syncthreads();
 #if WXB_TRACE_MAP
@@ -271,7 +284,7 @@ euler_traces(const EvalArgs a) {
         int base, step;
         line_of<N>(d, pt, base, step);
         double o[NTR];
-        extrap_line<N>(s_ext + side * N, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, o);
+        extrap_line<N>(s_ext + side * N, &s_q[le][0][0], P, &s_q[le][3][0], &s_q[le][4][0], base, step, a.fasttab, o);
         double* t = a.trace + (((long long)e * 6 + f) * NTR) * F + pt;  // [E][face][field][F]
 #pragma unroll
         for (int v = 0; v < NTR; ++v) t[v * F] = o[v];
@@ -288,7 +301,7 @@ euler_traces(const EvalArgs a) {
         int base, step;
         line_of<N>(d, pt, base, step);
         double lo[NTR], hi[NTR];
-        extrap_line2<N>(s_ext, &s_q[el][0][0], P, &s_q[el][3][0], &s_q[el][4][0], base, step, lo, hi);
+        extrap_line2<N>(s_ext, &s_q[el][0][0], P, &s_q[el][3][0], &s_q[el][4][0], base, step, a.fasttab, lo, hi);
         double* t = a.trace + (((long long)e2 * 6 + 2 * d) * NTR) * F + pt;  // [E][face][field][F]
 #pragma unroll
         for (int v = 0; v < NTR; ++v) {
@@ -351,7 +364,7 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     if (bc) uf = -uo;  // odd symmetry of w across the rigid boundary (pde_euler_cubesphere.py:152-156)
     constexpr double inv_gamma = 1.0 / WXB_GAMMA;
     const double po = own[5] * own[5] * (own[0] * inv_gamma), pf = nb[5] * nb[5] * (nb[0] * inv_gamma);  // a^2 rho / gamma
-    const double sh = sqrt(hdd);
+    const double sh = m_sqrt(hdd);
     const double eig = fmax(fabs(uo) + sh * own[5], fabs(uf) + sh * nb[5]);  // |u| + sqrt(h^dd gamma p / rho)
     const double sguo = sg * uo, sguf = sg * uf, es = side ? eig * sg : -(eig * sg);
     const double mo1 = own[0] * own[1], mo2 = own[0] * own[2], mo3 = own[0] * own[3];
@@ -361,7 +374,7 @@ __device__ __forceinline__ void rusanov_point(const EvalArgs& a, const ElemInfo&
     out[2] = 0.5 * ((sguo * mo2 + sg * hd1 * po) + (sguf * mf2 + sg * hd1 * pf) - es * (mf2 - mo2));
     out[3] = 0.5 * (sguo * own[4] + sguf * nb[4] - es * (nb[4] - own[4]));
     out[4] = 0.5 * (sguo * mo3 + sguf * mf3 - es * (mf3 - mo3));
-    out[5] = 0.5 * (sg * hd2 * po + sg * hd2 * pf) / po;
+    out[5] = 0.5 * (sg * hd2 * po + sg * hd2 * pf) * m_rcp(po);
 }
 #else
     double L[NTR], R[NTR];
@@ -635,13 +648,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
         }
         const double rho = q[0];
 #if WXB_RCP
-        const double irho = 1.0 / rho;
+        const double irho = m_rcp(rho);
         const double u1 = q[1] * irho, u2 = q[2] * irho, w = q[3] * irho;
 #else
         const double u1 = q[1] / rho, u2 = q[2] / rho, w = q[3] / rho;
 #endif
-        const double lg = log((WXB_RD / WXB_P0) * q[4]);
-        p = WXB_P0 * exp(WXB_GAMMA * lg);  // pde_euler_cubesphere.py:100
+        const double lg = m_log((WXB_RD / WXB_P0) * q[4], a.fasttab);
+        p = WXB_P0 * m_exp(WXB_GAMMA * lg, a.fasttab);  // pde_euler_cubesphere.py:100
         // forcing (pde_euler_cubesphere.py:203-290)
         {
             const double t11 = rho * u1 * u1 + h[0] * p, t12 = rho * u1 * u2 + h[1] * p, t13 = rho * u1 * w + h[2] * p;
@@ -728,7 +741,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS, Cfg<N>::MINB) euler_main(cons
     }
 
     // ---- assemble ----
-    const double inv_sg = 1.0 / sg;
+    const double inv_sg = m_rcp(sg);
     double r[NVAR];
     r[0] = -inv_sg * acc[0];
     r[1] = -inv_sg * acc[1] - fo[0];

@@ -77,6 +77,10 @@
 #ifndef WXB_SW_MINB6
 #define WXB_SW_MINB6 1
 #endif
+#ifndef WXB_SW_ALIAS
+#define WXB_SW_ALIAS 0  // 1: the flux fields share their shared memory with the halo rows and the spent own rows (two more
+                        // barriers per step, 30 KB less per block at n = 4: 3 resident blocks instead of 2)
+#endif
 #ifndef WXB_SW_PREFETCH
 #define WXB_SW_PREFETCH 1  // request the next level's metric block / state rows into L2 one step ahead
 #endif
@@ -124,12 +128,27 @@ struct FaceDesc {
 constexpr int R_M = 0, R_LRHO = 3, R_LRT = 4, NSTAGE = 5;  // staged rows: rho u1, rho u2, rho w, log rho, log(rho theta)
 constexpr int NFLUX = 20;  // per direction F_rho F_u1 F_u2 F_theta w_adv w_pres; then log(Rd/p0 rho theta), sqrtG rho
 
+// staged rows and flux fields in one array (doubles):
+//   so(b)  [NSTAGE][NE][P]  own elements of the levels of parity b   (written one step ahead, dead after `faces`)
+//   sh     [NSTAGE][NH][P]  halo elements of the current level       (dead after `faces`)
+//   fl(k)  [NFLUX][NE][P]   flux fields of the current level         (written by `nodes`, read by `assemble`)
+// WXB_SW_ALIAS: so(0) | sh | pad | so(1), and fl(k) starts at so(0) for even k, at sh for odd k: it overwrites the spent
+// own rows and the halo rows but never the rows staged for the next level.
+template <int N>
+struct SweepLayout {
+    using C = SCfg<N>;
+    static constexpr int SO = NSTAGE * C::NE * C::P, SH = NSTAGE * C::NH * C::P, FL = NFLUX * C::NE * C::P;
+    static constexpr int PAD = FL > SO + SH ? FL - SO - SH : 0;
+    static constexpr int TOTAL = WXB_SW_ALIAS ? 2 * SO + SH + PAD : 2 * SO + SH + FL;
+    __device__ static constexpr int so(int b) { return WXB_SW_ALIAS ? (b ? SO + SH + PAD : 0) : b * SO; }
+    __device__ static constexpr int sh() { return WXB_SW_ALIAS ? SO : 2 * SO; }
+    __device__ static constexpr int fl(int k) { return WXB_SW_ALIAS ? ((k & 1) ? SO : 0) : 2 * SO + SH; }
+};
+
 template <int N>
 struct SweepSmem {
     using C = SCfg<N>;
-    double so[2][NSTAGE][C::NE][C::P];  // own elements, by level parity
-    double sh[NSTAGE][C::NH][C::P];     // halo elements of the current level
-    double fl[NFLUX][C::NE][C::P];      // flux fields of the current level
+    alignas(16) double buf[SweepLayout<N>::TOTAL];
     double ffx[C::NXF][7][C::F];        // interface results per physical face: 5 common values, w_pres* / p of the
     double ffy[C::NYF][7][C::F];        //   min-side (L) element [5] and of the max-side (R) element [6]
     double ffu[C::NE][7][C::F];         // face above each own element
@@ -156,18 +175,42 @@ template <int N>
 __device__ __forceinline__ void form_trace(const double* __restrict__ mp, int rs, const double* __restrict__ ext, int base, int step,
                                            const double* __restrict__ etab, double out[NTR]) {
     double a1 = 0.0, a2 = 0.0, a3 = 0.0, l0 = 0.0, l4 = 0.0;
+    if (N % 2 == 0 && step == 1) {
+        // a line along x1 is N consecutive doubles (16-byte aligned for even N): 128-bit loads, and a warp reads whole
+        // contiguous rows instead of 8-byte words N apart (no bank conflicts); same fma order as below
+        const double2* x2 = reinterpret_cast<const double2*>(mp + base);
+        double xv[5][N];
 #pragma unroll
-    for (int m = 0; m < N; ++m) {
-        const double w = ext[m];
-        const double* x = mp + base + m * step;
-        a1 = fma(w, x[0], a1);
-        a2 = fma(w, x[rs], a2);
-        a3 = fma(w, x[2 * rs], a3);
-        l0 = fma(w, x[R_LRHO * rs], l0);
-        l4 = fma(w, x[R_LRT * rs], l4);
+        for (int r = 0; r < 5; ++r)
+#pragma unroll
+            for (int m = 0; m < N / 2; ++m) {
+                const double2 t = x2[(r * rs) / 2 + m];
+                xv[r][2 * m] = t.x;
+                xv[r][2 * m + 1] = t.y;
+            }
+#pragma unroll
+        for (int m = 0; m < N; ++m) {
+            const double w = ext[m];
+            a1 = fma(w, xv[0][m], a1);
+            a2 = fma(w, xv[1][m], a2);
+            a3 = fma(w, xv[2][m], a3);
+            l0 = fma(w, xv[3][m], l0);
+            l4 = fma(w, xv[4][m], l4);
+        }
+    } else {
+#pragma unroll
+        for (int m = 0; m < N; ++m) {
+            const double w = ext[m];
+            const double* x = mp + base + m * step;
+            a1 = fma(w, x[0], a1);
+            a2 = fma(w, x[rs], a2);
+            a3 = fma(w, x[2 * rs], a3);
+            l0 = fma(w, x[R_LRHO * rs], l0);
+            l4 = fma(w, x[R_LRT * rs], l4);
+        }
     }
     const double rho = wxbfm::fast_exp(l0, etab);
-    const double r = 1.0 / rho;
+    const double r = wxbfm::fast_rcp(rho);
     out[0] = rho;
     out[1] = a1 * r;
     out[2] = a2 * r;
@@ -190,7 +233,7 @@ __device__ __forceinline__ void rusanov_lr(int d, const double L[NTR], const dou
     if (mirR) uR = -uL;
     constexpr double inv_gamma = 1.0 / WXB_GAMMA;
     const double pL = L[5] * L[5] * (L[0] * inv_gamma), pR = R[5] * R[5] * (R[0] * inv_gamma);  // a^2 rho / gamma
-    const double sh = sqrt(hdd);
+    const double sh = wxbfm::fast_sqrt(hdd);
     const double eig = fmax(fabs(uL) + sh * L[5], fabs(uR) + sh * R[5]);  // |u| + sqrt(h^dd gamma p / rho)
     const double sguL = sg * uL, sguR = sg * uR, es = eig * sg;
     const double mL1 = L[0] * L[1], mL2 = L[0] * L[2], mL3 = L[0] * L[3];
@@ -201,8 +244,8 @@ __device__ __forceinline__ void rusanov_lr(int d, const double L[NTR], const dou
     c[3] = 0.5 * (sguL * L[4] + sguR * R[4] - es * (R[4] - L[4]));
     c[4] = 0.5 * (sguL * mL3 + sguR * mR3 - es * (mR3 - mL3));
     const double num = 0.5 * (sg * hd2 * pL + sg * hd2 * pR);
-    w5L = num / pL;
-    w5R = num / pR;
+    w5L = num * wxbfm::fast_rcp(pL);
+    w5R = num * wxbfm::fast_rcp(pR);
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -215,10 +258,12 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     constexpr int RSO = NE * P, RSH = NH * P;  // distance between staged rows (own / halo)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SweepSmem<N>& sm = *reinterpret_cast<SweepSmem<N>*>(smem_raw);
+    using LY = SweepLayout<N>;
+    double* const sbuf = sm.buf;
     const int tid = threadIdx.x, le = tid / P, node = tid - le * P;
     const double* const s_op = sm.op;
     const double* const ltab = sm.tab;
-    const double* const etab = sm.tab + 2 * WXB_LOGTAB_N;
+    const double* const etab = sm.tab + WXB_EXPTAB_OFF;
 
     // ---- once per tile -------------------------------------------------------------------------------
     for (int t = tid; t < C::NOPS; t += NT) sm.op[t] = a.ops[t];
@@ -312,48 +357,72 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     }
 
     // ---- stage: state rows -> momenta and logs in shared memory -----------------------------------------
-    auto stage_own = [&](int k) {
-        if (!active) return;
-        const long long o = qoff0 + (long long)k * lvl;
-        double x[NVAR];
+    // In two halves: the LOADS of the next step's rows (own elements of level ko, halo elements of level kh; -1 = none)
+    // are issued before the assemble phase of the current step, which hides their latency; logs and shared-memory
+    // stores follow after it.  HR = halo (element, node) pairs per thread.
+    constexpr int HR = (NH * P + NT - 1) / NT;
+    // JVP mode stages q + eps*v: twice the operands to hold, so there the rows are requested where they are used
+    // (register budget: 128 at two resident blocks)
+    constexpr bool EARLY = !JVP && HR <= 2;
+    double xo[NVAR], xh[HR][NVAR];
+    double vo[JVP ? NVAR : 1], vh[HR][JVP ? NVAR : 1];
+    auto halo_load1 = [&](int kh, int r) {
+        const int t = tid + r * NT;
+        const int h = t / P, hn = t - h * P;
+        if (t < NH * P && sm.hd[h].kind == 1) {
+            const HaloDesc& hd = sm.hd[h];
+            const long long o = hd.off0 + (long long)kh * hd.lvl + hn;
 #pragma unroll
-        for (int v = 0; v < NVAR; ++v) x[v] = a.q[o + v * vstride];
+            for (int v = 0; v < NVAR; ++v) xh[r][v] = a.q[o + v * hd.vstride];
+            if (JVP) {
+#pragma unroll
+                for (int v = 0; v < NVAR; ++v) vh[r][v] = a.v[o + v * hd.vstride];
+            }
+        }
+    };
+    auto halo_load = [&](int kh) {
+#pragma unroll
+        for (int r = 0; r < HR; ++r) halo_load1(kh, r);
+    };
+    auto own_load = [&](int ko) {
+        if (active && ko >= 0) {
+            const long long o = qoff0 + (long long)ko * lvl;
+#pragma unroll
+            for (int v = 0; v < NVAR; ++v) xo[v] = a.q[o + v * vstride];
+            if (JVP) {
+#pragma unroll
+                for (int v = 0; v < NVAR; ++v) vo[v] = a.v[o + v * vstride];
+            }
+        }
+    };
+    auto stage_load = [&](int ko, int kh) {
+        if (EARLY) {
+            own_load(ko);
+            if (kh >= 0) halo_load(kh);
+        }
+    };
+    auto stage_put = [&](double* dst, int rs, double x[NVAR], const double* dv) {
         if (JVP) {
-            double dv[NVAR];
-#pragma unroll
-            for (int v = 0; v < NVAR; ++v) dv[v] = a.v[o + v * vstride];
 #pragma unroll
             for (int v = 0; v < NVAR; ++v) x[v] += a.eps * dv[v];
         }
-        double* dst = &sm.so[k & 1][0][le][node];
         dst[0] = x[1];
-        dst[RSO] = x[2];
-        dst[2 * RSO] = x[3];
-        dst[R_LRHO * RSO] = wxbfm::fast_log(x[0], ltab);
-        dst[R_LRT * RSO] = wxbfm::fast_log(x[4], ltab);
+        dst[rs] = x[2];
+        dst[2 * rs] = x[3];
+        dst[R_LRHO * rs] = wxbfm::fast_log(x[0], ltab);
+        dst[R_LRT * rs] = wxbfm::fast_log(x[4], ltab);
     };
-    auto stage_halo = [&](int k) {
-        for (int t = tid; t < NH * P; t += NT) {
-            const int h = t / P, hn = t - h * P;
-            const HaloDesc& hd = sm.hd[h];
-            if (hd.kind != 1) continue;
-            const long long o = hd.off0 + (long long)k * hd.lvl + hn;
-            double x[NVAR];
+    auto stage_store = [&](int ko, int kh) {
+        if (!EARLY) own_load(ko);
+        if (active && ko >= 0) stage_put(sbuf + LY::so(ko & 1) + le * P + node, RSO, xo, vo);
+        if (kh >= 0) {
 #pragma unroll
-            for (int v = 0; v < NVAR; ++v) x[v] = a.q[o + v * hd.vstride];
-            if (JVP) {
-                double dv[NVAR];
-#pragma unroll
-                for (int v = 0; v < NVAR; ++v) dv[v] = a.v[o + v * hd.vstride];
-#pragma unroll
-                for (int v = 0; v < NVAR; ++v) x[v] += a.eps * dv[v];
+            for (int r = 0; r < HR; ++r) {
+                if (!EARLY) halo_load1(kh, r);
+                const int t = tid + r * NT;
+                const int h = t / P, hn = t - h * P;
+                if (t < NH * P && sm.hd[h].kind == 1) stage_put(sbuf + LY::sh() + h * P + hn, RSH, xh[r], vh[r]);
             }
-            double* dst = &sm.sh[0][h][hn];
-            dst[0] = x[1];
-            dst[RSH] = x[2];
-            dst[2 * RSH] = x[3];
-            dst[R_LRHO * RSH] = wxbfm::fast_log(x[0], ltab);
-            dst[R_LRT * RSH] = wxbfm::fast_log(x[4], ltab);
         }
     };
 
@@ -380,7 +449,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 int rs, dl, ptl, flags = 0;
                 const double* ghost = nullptr;
                 if (code < 100) {
-                    mp = &sm.so[k & 1][0][code][0];
+                    mp = sbuf + LY::so(k & 1) + code * P;
                     rs = RSO;
                     ext = s_op + own_side * N;
                     dl = d;
@@ -389,7 +458,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                     const HaloDesc& hd = sm.hd[code - 100];
                     flags = hd.flags;
                     ptl = (flags & 1) ? kl * N + (N - 1 - al) : pt;
-                    mp = &sm.sh[0][code - 100][0];
+                    mp = sbuf + LY::sh() + (code - 100) * P;
                     rs = RSH;
                     ext = s_op + (hd.fq & 1) * N;
                     dl = hd.fq >> 1;
@@ -416,8 +485,8 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 int base, step;
                 line_of<N>(2, pt, base, step);
                 const bool haveL = k >= 0, haveR = k + 1 < nz;
-                if (haveL) form_trace<N>(&sm.so[k & 1][0][lo][0], RSO, s_op + N, base, step, etab, L);
-                if (haveR) form_trace<N>(&sm.so[(k + 1) & 1][0][lo][0], RSO, s_op, base, step, etab, R);
+                if (haveL) form_trace<N>(sbuf + LY::so(k & 1) + lo * P, RSO, s_op + N, base, step, etab, L);
+                if (haveR) form_trace<N>(sbuf + LY::so((k + 1) & 1) + lo * P, RSO, s_op, base, step, etab, R);
                 if (!haveL) {  // rigid bottom: the ghost mirrors the real face (rhs_dfr.py:265-268)
 #pragma unroll
                     for (int v = 0; v < NTR; ++v) L[v] = R[v];
@@ -450,8 +519,13 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 
     const int k0 = a.k0, k1 = a.k1;
     __syncthreads();  // descriptors, operators, tables
-    if (k0 > 0) stage_own(k0 - 1);
-    stage_own(k0);
+    if (k0 > 0) {
+        stage_load(k0 - 1, -1);
+        stage_store(k0 - 1, -1);
+    }
+    stage_load(k0, -1);
+    stage_store(k0, -1);
+    stage_load(k0 + 1 < nz ? k0 + 1 : -1, k0);  // the first step's rows: in flight during the face pass below
     __syncthreads();
     faces(k0 - 1, true);  // the face below the first level (rigid bottom, or the level below a chunk)
     __syncthreads();
@@ -459,11 +533,9 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
     const long long EP = (long long)a.E * P;
     constexpr int RS = NE * P;
-    double* const col = &sm.fl[0][le][node];
 
     for (int k = k0; k < k1; ++k) {
-        if (k + 1 < nz) stage_own(k + 1);
-        stage_halo(k);
+        stage_store(k + 1 < nz ? k + 1 : -1, k);
 #if WXB_SW_PREFETCH
         if (active && k + 1 < k1) {  // next step's metric block (35 rows of this element, contiguous) and JVP operands into L2
             const char* mb = (const char*)(a.chris + (e0 + (long long)(k + 1) * ny * nx) * (35 * P));
@@ -480,6 +552,8 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 #endif
         __syncthreads();
         faces(k, false);
+        if (WXB_SW_ALIAS) __syncthreads();  // the flux fields overwrite rows the face pass reads
+        double* const col = sbuf + LY::fl(k) + le * P + node;
 
         // ---- nodes: forcing and the flux fields of the three directions -> own column of fl ----------------
         double sg = 1.0, p = 1.0, gfac = 0.0, fo[3] = {0.0, 0.0, 0.0};
@@ -504,7 +578,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 #pragma unroll
             for (int c = 0; c < 27; ++c) ch[c] = mrow[c * P];
             const double rho = q[0];
-            const double irho = 1.0 / rho;
+            const double irho = wxbfm::fast_rcp(rho);
             const double u1 = q[1] * irho, u2 = q[2] * irho, w = q[3] * irho;
             const double lg = wxbfm::fast_log((WXB_RD / WXB_P0) * q[4], ltab);
             p = WXB_P0 * wxbfm::fast_exp(WXB_GAMMA * lg, etab);  // pde_euler_cubesphere.py:100
@@ -543,6 +617,8 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
             col[19 * RS] = sg * rho;
         }
         __syncthreads();
+        // the next step's rows (own level k+2, halo level k+1): requested now, used after the assemble phase
+        if (k + 1 < k1) stage_load(k + 2 < nz ? k + 2 : -1, k + 1);
 
         if (active) {
             double r0[NVAR], vv[NVAR];
@@ -561,8 +637,8 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
                 const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
                 const int pt = d == 0 ? kk * N + jj : (d == 1 ? kk * N + ii : jj * N + ii);
-                const double* sfd = &sm.fl[d * 6][le][node - idx * step];
-                const double* slp = &sm.fl[18][le][node - idx * step];
+                const double* sfd = col + (d * 6) * RS - idx * step;
+                const double* slp = col + 18 * RS - idx * step;
                 double dv[7] = {0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
                 for (int m = 0; m < N; ++m) {
@@ -586,7 +662,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 const double wpres = col[(d * 6 + 5) * RS];
                 wacc += dv[4] + p * dv[5] + p * wpres * dv[6];
             }
-            const double inv_sg = 1.0 / sg;
+            const double inv_sg = wxbfm::fast_rcp(sg);
             double r[NVAR];
             r[0] = -inv_sg * acc[0];
             r[1] = -inv_sg * acc[1] - fo[0];
@@ -603,6 +679,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 a.out[qo + v * vstride] = x;
             }
         }
+        if (WXB_SW_ALIAS) __syncthreads();  // the next step stages rows where the flux fields were
     }
 }
 
@@ -649,7 +726,7 @@ __global__ void __launch_bounds__(N* N* N) euler_edge_traces(const EvalArgs a) {
         int base, step;
         line_of<N>(f >> 1, node, base, step);
         double o6[NTR];
-        form_trace<N>(&srow[0][0], P, s_ext + (f & 1) * N, base, step, s_tab + 2 * WXB_LOGTAB_N, o6);
+        form_trace<N>(&srow[0][0], P, s_ext + (f & 1) * N, base, step, s_tab + WXB_EXPTAB_OFF, o6);
         double* dst = a.sendbuf + (((long long)rec * a.nz + k) * NTR) * F + node;
 #pragma unroll
         for (int v = 0; v < NTR; ++v) dst[v * F] = o6[v];

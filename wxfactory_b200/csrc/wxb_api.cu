@@ -236,10 +236,12 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
         h->d_trace = h->sweep ? h->d_trace_alloc - h->trace_local : h->d_trace_alloc;
     }
     if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->ntr * nz * h->F * sizeof(double)));
-    if (h->sweep) {
+    if (euler) {  // log / exp tables of fastmath.cuh
         std::vector<double> tab(WXB_FASTTAB_DOUBLES);
         wxbfm::fill_tables(tab.data());
         UP(h->d_fasttab, tab.data(), tab.size());
+    }
+    if (h->sweep) {
         // tiles of TJ x TI columns, slab after slab, row-major; a tile is "outer" if one of its columns reads a ghost
         int tj = 1, ti = 1;
         wxb_sweep_tile_shape(n, &tj, &ti);

@@ -87,12 +87,16 @@ class TiledEulerProblem:
     def _node_field(self, part, arr, lead):
         """arr (6, *lead, bz*bh*bh, P) -> (*lead, E_local*P)."""
         a = arr.reshape((6,) + lead + (self.bz, self.bh, self.bh, self.P))
-        out = []
-        for sl in part.slabs:
+        counts = [self.nz * sl.ny * self.nh * self.P for sl in part.slabs]
+        out = numpy.empty(lead + (sum(counts),))  # filled slab by slab: the peak is the result + one slab (24 GB at s = 1)
+        off = 0
+        for sl, cnt in zip(part.slabs, counts):
             kk, jj, ii = self._kji(sl)
             blk = a[sl.panel][..., kk[:, None, None], jj[None, :, None], ii[None, None, :], :]
-            out.append(blk.reshape(lead + (-1,)))
-        return numpy.ascontiguousarray(numpy.concatenate(out, axis=-1))
+            out[..., off : off + cnt] = blk.reshape(lead + (-1,))
+            off += cnt
+            del blk
+        return out
 
     def local_static(self, part):
         """Same dict as layout.local_static for the slabs of `part`."""
