@@ -81,8 +81,19 @@
 #define WXB_SW_ALIAS 0  // 1: the flux fields share their shared memory with the halo rows and the spent own rows (two more
                         // barriers per step, 30 KB less per block at n = 4: 3 resident blocks instead of 2)
 #endif
+#ifndef WXB_SW_CH3
+#define WXB_SW_CH3 0  // 1: Christoffel symbols loaded 9 at a time where they are used (fewer registers, less memory parallelism)
+#endif
+#ifndef WXB_SW_SKIP
+#define WXB_SW_SKIP 0  // TIMING EXPERIMENTS ONLY (compile-time, never set in a shipped build; results are wrong): bit 0 skip
+                       // the face pass, 1 the node pass, 2 the assemble phase's arithmetic, 3 the halo staging
+#endif
 #ifndef WXB_SW_PREFETCH
-#define WXB_SW_PREFETCH 1  // request the next level's metric block / state rows into L2 one step ahead
+#define WXB_SW_PREFETCH 3  // request the metric block / state rows of a later level into L2: 0 off, 1 one prefetch.global.L2
+                           // per 128 bytes, 2 one per 32-byte sector, 3 one bulk prefetch per element (TMA engine)
+#endif
+#ifndef WXB_SW_PFDIST
+#define WXB_SW_PFDIST 1    // how many levels ahead
 #endif
 
 namespace {
@@ -249,6 +260,10 @@ __device__ __forceinline__ void rusanov_lr(int d, const double L[NTR], const dou
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// one instruction for a whole contiguous block (bytes: a multiple of 16, address 16-byte aligned)
+__device__ __forceinline__ void prefetch_bulk_l2(const void* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 
 // ------------------------------------------------------------------------------------------------------
 template <int N, bool JVP>
@@ -367,6 +382,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     double xo[NVAR], xh[HR][NVAR];
     double vo[JVP ? NVAR : 1], vh[HR][JVP ? NVAR : 1];
     auto halo_load1 = [&](int kh, int r) {
+        if (WXB_SW_SKIP & 8) return;
         const int t = tid + r * NT;
         const int h = t / P, hn = t - h * P;
         if (t < NH * P && sm.hd[h].kind == 1) {
@@ -421,7 +437,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 if (!EARLY) halo_load1(kh, r);
                 const int t = tid + r * NT;
                 const int h = t / P, hn = t - h * P;
-                if (t < NH * P && sm.hd[h].kind == 1) stage_put(sbuf + LY::sh() + h * P + hn, RSH, xh[r], vh[r]);
+                if (t < NH * P && sm.hd[h].kind == 1 && !(WXB_SW_SKIP & 8)) stage_put(sbuf + LY::sh() + h * P + hn, RSH, xh[r], vh[r]);
             }
         }
     };
@@ -537,31 +553,36 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     for (int k = k0; k < k1; ++k) {
         stage_store(k + 1 < nz ? k + 1 : -1, k);
 #if WXB_SW_PREFETCH
-        if (active && k + 1 < k1) {  // next step's metric block (35 rows of this element, contiguous) and JVP operands into L2
-            const char* mb = (const char*)(a.chris + (e0 + (long long)(k + 1) * ny * nx) * (35 * P));
-            for (int l = node * 128; l < 35 * P * 8; l += P * 128) prefetch_l2(mb + l);
-            if (k + 2 < nz && node < NVAR) {  // the state rows staged by the next step
-                const char* qb = (const char*)(a.q + qoff0 - node + (long long)(k + 2) * lvl + node * vstride);
-                for (int l = 0; l < P * 8; l += 128) prefetch_l2(qb + l);
+        if (active && k + WXB_SW_PFDIST < k1) {  // a later step's metric block (35 rows of this element, contiguous) into L2
+            const char* mb = (const char*)(a.chris + (e0 + (long long)(k + WXB_SW_PFDIST) * ny * nx) * (35 * P));
+            constexpr int PFS = WXB_SW_PREFETCH == 2 ? 32 : 128;
+            if (WXB_SW_PREFETCH == 3 && (35 * P * 8) % 16 == 0) {  // bulk form: 16-byte granularity (even n)
+                if (node == 0) prefetch_bulk_l2(mb, 35 * P * 8);
+            } else {
+                for (int l = node * PFS; l < 35 * P * 8; l += P * PFS) prefetch_l2(mb + l);
+            }
+            if (k + 1 + WXB_SW_PFDIST < nz && node < NVAR) {  // the state rows staged by that step
+                const char* qb = (const char*)(a.q + qoff0 - node + (long long)(k + 1 + WXB_SW_PFDIST) * lvl + node * vstride);
+                for (int l = 0; l < P * 8; l += PFS) prefetch_l2(qb + l);
                 if (JVP) {
-                    const char* vb = (const char*)(a.v + qoff0 - node + (long long)(k + 2) * lvl + node * vstride);
-                    for (int l = 0; l < P * 8; l += 128) prefetch_l2(vb + l);
+                    const char* vb = (const char*)(a.v + qoff0 - node + (long long)(k + 1 + WXB_SW_PFDIST) * lvl + node * vstride);
+                    for (int l = 0; l < P * 8; l += PFS) prefetch_l2(vb + l);
                 }
             }
         }
 #endif
         __syncthreads();
-        faces(k, false);
+        if (!(WXB_SW_SKIP & 1)) faces(k, false);
         if (WXB_SW_ALIAS) __syncthreads();  // the flux fields overwrite rows the face pass reads
         double* const col = sbuf + LY::fl(k) + le * P + node;
 
         // ---- nodes: forcing and the flux fields of the three directions -> own column of fl ----------------
         double sg = 1.0, p = 1.0, gfac = 0.0, fo[3] = {0.0, 0.0, 0.0};
         const long long qo = qoff0 + (long long)k * lvl;
-        if (active) {
+        if (active && !(WXB_SW_SKIP & 2)) {
             const long long e = e0 + (long long)k * ny * nx;
             const double* const mrow = a.chris + e * (35 * P) + node;  // [35][P]: Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta
-            double q[NVAR], h[6], ch[27];
+            double q[NVAR], h[6], ch[WXB_SW_CH3 ? 1 : 27];
 #pragma unroll
             for (int v = 0; v < NVAR; ++v) q[v] = a.q[qo + v * vstride];
             if (JVP) {
@@ -575,8 +596,10 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 #pragma unroll
             for (int c = 0; c < 6; ++c) h[c] = mrow[(28 + c) * P];
             gfac = mrow[34 * P];
+            if (!WXB_SW_CH3) {
 #pragma unroll
-            for (int c = 0; c < 27; ++c) ch[c] = mrow[c * P];
+                for (int c = 0; c < 27; ++c) ch[c] = mrow[c * P];
+            }
             const double rho = q[0];
             const double irho = wxbfm::fast_rcp(rho);
             const double u1 = q[1] * irho, u2 = q[2] * irho, w = q[3] * irho;
@@ -587,7 +610,9 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 const double t22 = rho * u2 * u2 + h[3] * p, t23 = rho * u2 * w + h[4] * p, t33 = rho * w * w + h[5] * p;
 #pragma unroll
                 for (int i = 0; i < 3; ++i) {
-                    const double* c = ch + 9 * i;
+                    double c[9];
+#pragma unroll
+                    for (int m = 0; m < 9; ++m) c[m] = WXB_SW_CH3 ? mrow[(9 * i + m) * P] : ch[WXB_SW_CH3 ? 0 : 9 * i + m];
                     fo[i] = 2.0 * rho * (c[0] * u1 + c[1] * u2 + c[2] * w) + c[3] * t11 + 2.0 * c[4] * t12 + 2.0 * c[5] * t13 +
                             c[6] * t22 + 2.0 * c[7] * t23 + c[8] * t33;
                 }
@@ -633,20 +658,39 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
             // ---- interior derivative (sum-factorised) + lift ----
             double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc = 0.0, grav = 0.0;
 #pragma unroll
-            for (int d = 0; d < 3; ++d) {
+            for (int d = 0; d < ((WXB_SW_SKIP & 4) ? 0 : 3); ++d) {
                 const int idx = d == 0 ? ii : (d == 1 ? jj : kk);
                 const int step = d == 0 ? 1 : (d == 1 ? N : N * N);
                 const int pt = d == 0 ? kk * N + jj : (d == 1 ? kk * N + ii : jj * N + ii);
                 const double* sfd = col + (d * 6) * RS - idx * step;
                 const double* slp = col + 18 * RS - idx * step;
                 double dv[7] = {0, 0, 0, 0, 0, 0, 0};
+                if (d == 0 && N % 2 == 0) {
+                    // a line along x1 is N consecutive doubles, 16-byte aligned: 128-bit loads (same sums, same order)
+                    const double2* s2 = reinterpret_cast<const double2*>(sfd);
+                    const double2* l2 = reinterpret_cast<const double2*>(slp);
 #pragma unroll
-                for (int m = 0; m < N; ++m) {
-                    const double dm = s_op[C::O_DIFF + idx * N + m];
+                    for (int m = 0; m < N; m += 2) {
+                        const double d0 = s_op[C::O_DIFF + idx * N + m], d1 = s_op[C::O_DIFF + idx * N + m + 1];
 #pragma unroll
-                    for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * RS + m * step];
-                    dv[6] += s_op[C::O_DLP + idx * N + m] * slp[m * step];
-                    if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[RS + m * step];
+                        for (int v = 0; v < 6; ++v) {
+                            const double2 t = s2[(v * RS + m) / 2];
+                            dv[v] += d0 * t.x;
+                            dv[v] += d1 * t.y;
+                        }
+                        const double2 t = l2[m / 2];
+                        dv[6] += s_op[C::O_DLP + idx * N + m] * t.x;
+                        dv[6] += s_op[C::O_DLP + idx * N + m + 1] * t.y;
+                    }
+                } else {
+#pragma unroll
+                    for (int m = 0; m < N; ++m) {
+                        const double dm = s_op[C::O_DIFF + idx * N + m];
+#pragma unroll
+                        for (int v = 0; v < 6; ++v) dv[v] += dm * sfd[v * RS + m * step];
+                        dv[6] += s_op[C::O_DLP + idx * N + m] * slp[m * step];
+                        if (d == 2) grav += s_op[C::O_HF + idx * N + m] * slp[RS + m * step];
+                    }
                 }
                 const double cw = s_op[C::O_CORR + idx * 2], ce = s_op[C::O_CORR + idx * 2 + 1];
                 const double* flo = d == 0 ? &sm.ffx[sa * (TI + 1) + sb][0][pt] : (d == 1 ? &sm.ffy[sa * TI + sb][0][pt] : &sm.ffd[le][0][pt]);

@@ -11,8 +11,10 @@
 
 #ifdef __CUDACC__
 #define WXB_HD __host__ __device__ __forceinline__
+#define WXB_FM __device__ __forceinline__  // the math functions read __constant__ coefficients: device-only under nvcc
 #else
 #define WXB_HD inline
+#define WXB_FM inline                      // plain C++ build (tests/test_fastmath.py): the same code on the host
 #endif
 #include <cmath>
 #include <cstring>
@@ -81,7 +83,7 @@ WXB_FM_CONST FM_C[16] = {
 #define WXB_FM_LIB_DIV 0
 #endif
 
-WXB_HD double fast_log(double x, const double* __restrict__ tab) {
+WXB_FM double fast_log(double x, const double* __restrict__ tab) {
     if (WXB_FM_LIB_LOG) return log(x);
     const uint64_t ix = bits_of(x);
     const uint32_t top = (uint32_t)(ix >> 32);
@@ -110,7 +112,7 @@ WXB_HD double fast_log(double x, const double* __restrict__ tab) {
 
 // e^x; tab = the 64 values 2^(j/64).  BRANCH-FREE and unguarded: valid for |x| < 700 (the kernels feed it extrapolated
 // logs of physical densities); NaN and +-inf give NaN.
-WXB_HD double fast_exp(double x, const double* __restrict__ tab) {
+WXB_FM double fast_exp(double x, const double* __restrict__ tab) {
     if (WXB_FM_LIB_EXP) return exp(x);
     double kd = fma(x, FM_C[7], FM_C[14]);  // x * 64/ln2, rounded to an integer in the low mantissa bits
     const uint64_t ki = bits_of(kd);
@@ -128,7 +130,7 @@ WXB_HD double fast_exp(double x, const double* __restrict__ tab) {
 
 // 1/x and sqrt(x) without the library's special-case branches (one MUFU seed + Newton steps; within 1-2 ulp for
 // normal positive x, NaN for 0 / inf / NaN where the library would give inf / 0)
-WXB_HD double fast_rcp(double x) {
+WXB_FM double fast_rcp(double x) {
     if (WXB_FM_LIB_DIV) return 1.0 / x;
 #ifdef __CUDA_ARCH__
     double r;
@@ -141,7 +143,7 @@ WXB_HD double fast_rcp(double x) {
     return 1.0 / x;
 #endif
 }
-WXB_HD double fast_sqrt(double x) {
+WXB_FM double fast_sqrt(double x) {
     if (WXB_FM_LIB_DIV) return sqrt(x);
 #ifdef __CUDA_ARCH__
     double y;

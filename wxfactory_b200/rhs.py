@@ -354,7 +354,7 @@ def matvec_fun(vec, dt, Q, rhs, rhs_handle, method="fd"):
     if method == "complex":
         raise TypeError("complex-step JVP is not available on the B200 path: set jacobian_method = fd")
     owner = getattr(rhs_handle, "__self__", rhs_handle)
-    if isinstance(owner, RhsB200):
+    if isinstance(owner, (RhsB200, _PerRankRhs)):
         return owner.jvp(vec, dt, Q, rhs, mode="fd")
     Qvec = Q + EPS_FD * vec.reshape(Q.shape)
     jac = dt * (rhs_handle(Qvec) - rhs) / EPS_FD
@@ -364,7 +364,7 @@ def matvec_fun(vec, dt, Q, rhs, rhs_handle, method="fd"):
 def matvec_rat(vec, dt, Q, rhs, rhs_handle):
     """wx_factory/solvers/matvec.py:76-88."""
     owner = getattr(rhs_handle, "__self__", rhs_handle)
-    if isinstance(owner, RhsB200):
+    if isinstance(owner, (RhsB200, _PerRankRhs)):
         return owner.jvp(vec, dt, Q, rhs, mode="rat")
     Qvec = Q + EPS_FD * vec.reshape(Q.shape)
     jac = dt * (rhs_handle(Qvec) - rhs) / EPS_FD
@@ -435,25 +435,105 @@ class MatvecOpFd(MatvecOpRat):
         return MatvecOpB200.__call__(self, vec)
 
 
+class _PerRankRhs:
+    """``RhsBundle.full`` of ONE rank of the reference's 6-rank MPI job when the whole sphere lives on one B200 owned by
+    rank 0: ``rhs(q_local)`` gathers the six local states on rank 0 (``comm.gather``), evaluates there through the C
+    ABI and scatters dQ/dt back, so every rank gets its own panel's result with ``RHS.__call__``'s contract (any shape
+    in, same shape out, fresh array; wx_factory/rhs/rhs.py:75-122).  Collective: every rank must call it the same number
+    of times, as with the reference (wx_factory/rhs/rhs_euler.py:180-181)."""
+
+    def __init__(self, comm, owner, local_size, root=0):
+        self.comm, self.owner, self.root, self.local_size = comm, owner, root, int(local_size)
+        self.rank = comm.Get_rank()
+        self.timings, self.timestamps = [], []
+
+    def _collective(self, arrays, fn):
+        """Gather the tuple of local arrays of every rank, apply fn(list of stacked arrays) on the root, scatter."""
+        shape = arrays[0].shape
+        for x in arrays:
+            if numpy.iscomplexobj(x):
+                raise TypeError("complex state: the B200 path implements the finite-difference JVP only (jacobian_method = fd)")
+            if x.size != self.local_size:
+                raise ValueError(f"array has {x.size} values, this rank's RHS expects {self.local_size}")
+        parts = self.comm.gather(tuple(numpy.asarray(x, dtype=numpy.float64).reshape(-1) for x in arrays), root=self.root)
+        out = None
+        if self.rank == self.root:
+            stacked = [numpy.stack([p[i] for p in parts]) for i in range(len(arrays))]
+            res = numpy.asarray(fn(*stacked)).reshape(len(parts), -1)
+            out = [res[r].copy() for r in range(len(parts))]
+        return self.comm.scatter(out, root=self.root).reshape(shape)
+
+    def __call__(self, q):
+        return self._collective((q,), lambda Q: self.owner(Q))
+
+    def full(self, q):
+        return self(q)
+
+    def jvp(self, vec, dt, Q, rhs0, mode="fd", eps=EPS_FD):
+        vec = numpy.asarray(vec)
+        out = self._collective((vec.reshape(numpy.shape(Q)), Q, rhs0), lambda V, QQ, R: self.owner.jvp(V, dt, QQ, R, mode=mode, eps=eps))
+        return out.reshape(-1)
+
+    def retrieve_last_times(self):
+        if self.rank == self.root:
+            self.owner.retrieve_last_times()
+            self.timings = self.owner.timings
+
+    def clear_timings(self):
+        self.timings, self.timestamps = [], []
+        if self.rank == self.root:
+            self.owner.clear_timings()
+
+    def print_times(self):
+        if self.rank == self.root:
+            self.owner.print_times()
+
+
 class RhsBundleB200:
     """wx_factory/rhs/rhs_selector.py:18-84: ``.full`` is the RHS callable handed to every integrator
-    (wx_factory/simulation/simulation.py:336-395).  ``ranks`` = the 6 per-panel reference objects
-    (geom, ops, metric, config[, topo]); see from_reference.py."""
+    (wx_factory/simulation/simulation.py:336-395).  Two ways to build it:
 
-    def __init__(self, ranks, device=0):
-        from .from_reference import problem_from_reference
+    * ``RhsBundleB200(geom, operators, metric, topo, ptopo, param, fields_shape)`` -- the reference's own argument list,
+      called by EVERY rank of its 6-rank MPI job where ``RhsBundle(...)`` stands (simulation.py:111).  The static
+      arrays are gathered on rank 0 (``from_reference.gather_to_one_process``, ``ptopo.comm``), which owns the device
+      handle; ``.full(q_local)`` is collective (gather states, evaluate, scatter).
+    * ``RhsBundleB200(ranks, device=0)`` -- all six per-panel objects (geom, ops, metric, config[, topo]) in one
+      process; ``.full`` takes the stacked state ``(6, nvar, ...)`` or anything of that size.
+    """
 
-        eq = str(ranks[0].config.equations).lower()
-        if eq not in ("euler", "shallow_water"):
-            raise ValueError(f"Unrecognized combination of equations ({eq}) and geometry")
-        self.problem = problem_from_reference(ranks)
-        self.full = RhsB200(self.problem, device=device)
-        self.shape = self.problem.state_shape
+    rhs_class = None  # the class that owns the device handle (RhsB200); tests substitute an oracle-backed stand-in
+
+    def __init__(self, geom, operators=None, metric=None, topo=None, ptopo=None, param=None, fields_shape=None, debug=False, device=0, comm=None):
+        from .from_reference import gather_to_one_process, problem_from_reference
+
+        make = self.rhs_class or RhsB200
+
+        ops0 = None
+        if operators is None and param is None:  # all six panels' objects in this process
+            ranks = geom
+            eq = str(ranks[0].config.equations).lower()
+            if eq not in ("euler", "shallow_water"):
+                raise ValueError(f"Unrecognized combination of equations ({eq}) and geometry")
+            self.problem = problem_from_reference(ranks)
+            self.owner = make(self.problem, device=device)
+            self.full = self.owner
+            self.shape = self.problem.state_shape
+            ops0 = getattr(ranks[0], "ops", None)
+        else:  # one rank of the reference's 6-rank job
+            eq = str(param.equations).lower()
+            if eq not in ("euler", "shallow_water"):
+                raise ValueError(f"Unrecognized combination of equations ({eq}) and geometry ({type(geom)})")
+            if comm is None:
+                comm = ptopo.comm
+            self.shape = tuple(fields_shape)
+            self.problem = gather_to_one_process(geom, operators, metric, param, topo, comm=comm)
+            self.owner = make(self.problem, device=device) if self.problem is not None else None
+            self.full = _PerRankRhs(comm, self.owner, int(numpy.prod(self.shape)))
+            ops0 = operators
         # the per-step exponential filter of the same operators object, when the configuration applies one
         # (DFROperators.expfilter_apply, wx_factory/geometry/operators.py:101-119)
         self.filter = None
-        ops0 = getattr(ranks[0], "ops", None)
-        if eq == "euler" and getattr(ops0, "expfilter_apply", False):
+        if eq == "euler" and getattr(ops0, "expfilter_apply", False) and self.owner is not None:
             from .stepops import ExpFilterB200
 
-            self.filter = ExpFilterB200(self.full, numpy.asarray(ops0.expfilter, dtype=float))
+            self.filter = ExpFilterB200(self.owner, numpy.asarray(ops0.expfilter, dtype=float))
