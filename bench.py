@@ -401,9 +401,6 @@ def run_b200(args):
     torch.cuda.synchronize()
 
     def step_host():
-        if world > 1:  # multi-rank handles: numpy in / out through the device path (H2D, halo exchange, D2H)
-            out = rhs(q_h.numpy())
-            return rhs.jvp(v_h.numpy(), dt, q_h.numpy(), out, mode="fd")
         op = rhs.linearize(q_h.numpy(), dt, mode="fd")  # RHS(Q) comes back; (Q, RHS(Q)) stay as the operator's point
         return op.rhs, op(v_h.numpy())
 
@@ -515,7 +512,7 @@ def run_b200(args):
             "e2e": {
                 "value": 2.0 * total_dofs * e2e_steps / (ms_e2e * 1e-3),
                 "unit": UNIT,
-                "h2d_bytes_per_step": (2 if world == 1 else 4) * state_bytes,
+                "h2d_bytes_per_step": 2 * state_bytes,
                 "d2h_bytes_per_step": 2 * state_bytes,
                 "steps": e2e_steps,
                 "ms_per_step": ms_e2e / e2e_steps,
@@ -524,7 +521,8 @@ def run_b200(args):
                     "linearisation point, as MatvecOp captures them]; op(v numpy) [v up, J v down] -> wxb_linearize_host / "
                     "wxb_jvp_bound_host, state moved in chunks of levels on 3 streams; pinned host arrays in, numpy out"
                     if world == 1
-                    else "RhsB200.__call__(numpy) + RhsB200.jvp(numpy...): H2D of Q / v, Q, rhs0, halo exchange, D2H"
+                    else "op = RhsB200.linearize(Q numpy, dt) [Q up, RHS(Q) down, both kept on the device with the operator]; op(v numpy) "
+                    "[v up, J v down]; whole-state copies from / to pinned host arrays around wxb_eval_dist (halo exchange inside)"
                 ),
             },
             "gpu_launches": int(launches),

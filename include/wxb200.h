@@ -149,6 +149,29 @@ int wxb_traces(wxb_handle* h, const double* q, const double* v, double eps, void
 int wxb_finish(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps,
                int mode /* -1 = plain RHS */, int part, double* out, void* stream);
 
+/* Halo exchange inside the library (multi-GPU: one handle per process / GPU).  Replaces the MPI neighbour all-to-alls of
+ * ProcessTopology.start_exchange_scalars / start_exchange_vectors (wx_factory/process_topology.py:269-386) and the
+ * start_communication / end_communication pair of the RHS (wx_factory/rhs/rhs_dfr.py:141-201).
+ *   wxb_comm_unique_id : rank 0 fills a WXB_NCCL_ID_BYTES buffer (ncclGetUniqueId) and ships it to the other ranks by any
+ *                        means (MPI_Bcast, torch.distributed, a file)
+ *   wxb_comm_init      : every rank joins with (id, rank, nranks) and says which contiguous runs of its send records go
+ *                        to which rank, and which runs of its ghost records come from which rank (record = ntr*nz*F
+ *                        doubles; `first` / `count` in records, runs in buffer order)
+ *   wxb_exchange       : ncclGroupStart; ncclSend / ncclRecv per peer; ncclGroupEnd on `stream` (send buffer -> the
+ *                        peers' ghost records)
+ *   wxb_eval_dist      : one whole evaluation on such a handle: boundary traces, the exchange on the handle's own
+ *                        communication stream overlapped with the part that reads no ghost record, then the rest.
+ *                        mode -1: out = RHS(q) (v, rhs0 ignored); WXB_JVP_*: as wxb_jvp.
+ * NCCL is loaded with dlopen("libnccl.so.2") at the first call; the library has no link-time dependency on it. */
+#define WXB_NCCL_ID_BYTES 128
+int wxb_comm_unique_id(void* id_out);
+int wxb_comm_init(wxb_handle* h, const void* id, int rank, int nranks, int n_send_peers, const int32_t* send_peer,
+                  const int32_t* send_first, const int32_t* send_count, int n_recv_peers, const int32_t* recv_peer,
+                  const int32_t* recv_first, const int32_t* recv_count);
+int wxb_exchange(wxb_handle* h, void* stream);
+int wxb_eval_dist(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode,
+                  double* out, void* stream);
+
 /* Same as wxb_rhs / wxb_jvp with HOST buffers: H2D copy, kernels, D2H copy, synchronise.  For the 3-D Euler
  * equations the state moves in chunks of vertical levels on three streams, so that the upload of one chunk, the
  * kernels of the previous one and the download of the one before overlap (env WXB_HOST_CHUNKS, default 12;

@@ -184,7 +184,11 @@ def test_restart_round_trip_with_a_live_handle(golden, tmp_path):
         q = torch.from_numpy(local).cuda()
         r0 = rhs(q)
         assert rel(r0.cpu().numpy().reshape(ex["rhs0"].shape), ex["rhs0"]) <= RHS_TOL
-        name = state_io.write_restart(rhs, q, content, str(tmp_path), 7, 25.0)  # device tensor in
+        # the INI text is stored verbatim after the version line (load_state hands it back stripped): recover it from the file
+        raw = open(ref_file, "rb").read()
+        verbatim = raw[len(state_io.dumps(ex["Q0"], "", state_io.load_state(ref_file)[1])):].decode("utf-8")
+        assert verbatim.split()[:8] == content.split()[:8]
+        name = state_io.write_restart(rhs, q, verbatim, str(tmp_path), 7, 25.0)  # device tensor in
         assert os.path.basename(name) == os.path.basename(ref_file)
         assert open(name, "rb").read() == open(ref_file, "rb").read()
         again, _ = state_io.read_restart(rhs, name)

@@ -64,6 +64,7 @@ class WxbStaticArrays(ctypes.Structure):
 
 
 WXB_VEC_MAX_ROWS = 64  # include/wxb200.h
+WXB_NCCL_ID_BYTES = 128
 
 EXPORTS = [
     "wxb_version",
@@ -79,6 +80,10 @@ EXPORTS = [
     "wxb_jvp",
     "wxb_traces",
     "wxb_finish",
+    "wxb_comm_unique_id",
+    "wxb_comm_init",
+    "wxb_exchange",
+    "wxb_eval_dist",
     "wxb_rhs_host",
     "wxb_jvp_host",
     "wxb_linearize_host",
@@ -127,6 +132,10 @@ def load():
     lib.wxb_jvp.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp, vp]
     lib.wxb_traces.argtypes = [vp, vp, vp, dbl, vp]
     lib.wxb_finish.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, i32, vp, vp]
+    lib.wxb_comm_unique_id.argtypes = [vp]
+    lib.wxb_comm_init.argtypes = [vp, vp, i32, i32, i32, vp, vp, vp, i32, vp, vp, vp]
+    lib.wxb_exchange.argtypes = [vp, vp]
+    lib.wxb_eval_dist.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp, vp]
     lib.wxb_rhs_host.argtypes = [vp, vp, vp]
     lib.wxb_jvp_host.argtypes = [vp, vp, vp, vp, dbl, dbl, i32, vp]
     lib.wxb_linearize_host.argtypes = [vp, vp, vp]

@@ -81,6 +81,11 @@
 #define WXB_SW_ALIAS 0  // 1: the flux fields share their shared memory with the halo rows and the spent own rows (two more
                         // barriers per step, 30 KB less per block at n = 4: 3 resident blocks instead of 2)
 #endif
+#ifndef WXB_SW_SPLITORDER
+#define WXB_SW_SPLITORDER 1  // half of the block's warps run the node pass before the face pass, the other half after it:
+                             // the node pass waits for 40 loads per thread, the face pass is arithmetic on shared memory, so
+                             // each half's loads fly while the other half computes (needs WXB_SW_ALIAS = 0)
+#endif
 #ifndef WXB_SW_CH3
 #define WXB_SW_CH3 0  // 1: Christoffel symbols loaded 9 at a time where they are used (fewer registers, less memory parallelism)
 #endif
@@ -170,26 +175,34 @@ struct SweepSmem {
     FaceDesc fd[C::NFACE];
 };
 
-// line of face point pt of direction d: first node and node stride (x1-face pt = (k,j), x2-face (k,i), x3-face (j,i))
+// Staged element rows are stored SWIZZLED: node (k, j, i) of an element sits at k n^2 + ((j + k) mod n) n + i.  With the
+// plain order the 16 lines an x2-face reads (one per (k, i), n = 4) start 16 doubles = 32 banks apart for successive k
+// and collide 4-way in shared memory; rotating j by k spreads them over all banks, and the lines along x1 stay
+// contiguous (128-bit loads) and those along x3 conflict-free.
 template <int N>
-__device__ __forceinline__ void line_of(int d, int pt, int& base, int& step) {
-    const int a1 = pt / N, a0 = pt - a1 * N;
-    if (d == 0) { base = a1 * N * N + a0 * N; step = 1; }
-    else if (d == 1) { base = a1 * N * N + a0; step = N; }
-    else { base = a1 * N + a0; step = N * N; }
+__device__ __forceinline__ int swz(int k, int j, int i) {
+    int t = j + k;
+    t -= t >= N ? N : 0;
+    return k * N * N + t * N + i;
+}
+template <int N>
+__device__ __forceinline__ int swz_node(int node) {
+    const int k = node / (N * N), r = node - k * N * N, j = r / N;
+    return swz<N>(k, j, r - j * N);
 }
 
 // one trace point from the staged rows of an element (rows `rs` apart): extrapolation of the momenta and of the two
-// logs along the line (operators.py:161-165), then the fields the flux consumes: rho, u1, u2, w, rho theta and the
-// sound speed a = sqrt(gamma p / rho) = sqrt(gamma p0) exp((gamma (log(rho theta) + log(Rd/p0)) - log rho) / 2)
+// logs along the line of face point pt = c1*n + c0 of direction d (x1-face pt = (k,j), x2-face (k,i), x3-face (j,i);
+// operators.py:161-165), then the fields the flux consumes: rho, u1, u2, w, rho theta and the sound speed
+// a = sqrt(gamma p / rho) = sqrt(gamma p0) exp((gamma (log(rho theta) + log(Rd/p0)) - log rho) / 2)
 template <int N>
-__device__ __forceinline__ void form_trace(const double* __restrict__ mp, int rs, const double* __restrict__ ext, int base, int step,
+__device__ __forceinline__ void form_trace(const double* __restrict__ mp, int rs, const double* __restrict__ ext, int d, int pt,
                                            const double* __restrict__ etab, double out[NTR]) {
+    const int c1 = pt / N, c0 = pt - c1 * N;
     double a1 = 0.0, a2 = 0.0, a3 = 0.0, l0 = 0.0, l4 = 0.0;
-    if (N % 2 == 0 && step == 1) {
-        // a line along x1 is N consecutive doubles (16-byte aligned for even N): 128-bit loads, and a warp reads whole
-        // contiguous rows instead of 8-byte words N apart (no bank conflicts); same fma order as below
-        const double2* x2 = reinterpret_cast<const double2*>(mp + base);
+    if (N % 2 == 0 && d == 0) {
+        // a line along x1 is N consecutive doubles (16-byte aligned for even N): 128-bit loads; same fma order as below
+        const double2* x2 = reinterpret_cast<const double2*>(mp + swz<N>(c1, c0, 0));
         double xv[5][N];
 #pragma unroll
         for (int r = 0; r < 5; ++r)
@@ -212,7 +225,7 @@ __device__ __forceinline__ void form_trace(const double* __restrict__ mp, int rs
 #pragma unroll
         for (int m = 0; m < N; ++m) {
             const double w = ext[m];
-            const double* x = mp + base + m * step;
+            const double* x = mp + (d == 0 ? swz<N>(c1, c0, m) : (d == 1 ? swz<N>(c1, m, c0) : swz<N>(m, c1, c0)));
             a1 = fma(w, x[0], a1);
             a2 = fma(w, x[rs], a2);
             a3 = fma(w, x[2 * rs], a3);
@@ -430,14 +443,14 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     };
     auto stage_store = [&](int ko, int kh) {
         if (!EARLY) own_load(ko);
-        if (active && ko >= 0) stage_put(sbuf + LY::so(ko & 1) + le * P + node, RSO, xo, vo);
+        if (active && ko >= 0) stage_put(sbuf + LY::so(ko & 1) + le * P + swz_node<N>(node), RSO, xo, vo);
         if (kh >= 0) {
 #pragma unroll
             for (int r = 0; r < HR; ++r) {
                 if (!EARLY) halo_load1(kh, r);
                 const int t = tid + r * NT;
                 const int h = t / P, hn = t - h * P;
-                if (t < NH * P && sm.hd[h].kind == 1 && !(WXB_SW_SKIP & 8)) stage_put(sbuf + LY::sh() + h * P + hn, RSH, xh[r], vh[r]);
+                if (t < NH * P && sm.hd[h].kind == 1 && !(WXB_SW_SKIP & 8)) stage_put(sbuf + LY::sh() + h * P + swz_node<N>(hn), RSH, xh[r], vh[r]);
             }
         }
     };
@@ -484,9 +497,7 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 #pragma unroll
                     for (int v = 0; v < NTR; ++v) out[v] = ghost[v * F];
                 } else {
-                    int base, step;
-                    line_of<N>(dl, ptl, base, step);
-                    form_trace<N>(mp, rs, ext, base, step, etab, out);
+                    form_trace<N>(mp, rs, ext, dl, ptl, etab, out);
                 }
                 const int xid = flags >> 8;
                 if (xid) {  // the neighbour's (u1, u2) in this panel's basis (process_topology.py:138-175)
@@ -498,11 +509,9 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
                 }
             };
             if (d == 2) {
-                int base, step;
-                line_of<N>(2, pt, base, step);
                 const bool haveL = k >= 0, haveR = k + 1 < nz;
-                if (haveL) form_trace<N>(sbuf + LY::so(k & 1) + lo * P, RSO, s_op + N, base, step, etab, L);
-                if (haveR) form_trace<N>(sbuf + LY::so((k + 1) & 1) + lo * P, RSO, s_op, base, step, etab, R);
+                if (haveL) form_trace<N>(sbuf + LY::so(k & 1) + lo * P, RSO, s_op + N, 2, pt, etab, L);
+                if (haveR) form_trace<N>(sbuf + LY::so((k + 1) & 1) + lo * P, RSO, s_op, 2, pt, etab, R);
                 if (!haveL) {  // rigid bottom: the ghost mirrors the real face (rhs_dfr.py:265-268)
 #pragma unroll
                     for (int v = 0; v < NTR; ++v) L[v] = R[v];
@@ -572,13 +581,18 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
         }
 #endif
         __syncthreads();
-        if (!(WXB_SW_SKIP & 1)) faces(k, false);
-        if (WXB_SW_ALIAS) __syncthreads();  // the flux fields overwrite rows the face pass reads
+        constexpr bool SPLIT = WXB_SW_SPLITORDER && !WXB_SW_ALIAS;
+        const bool node_first = SPLIT && ((tid >> 5) & 4);  // warps 4..7 of every 8: one of each kind per scheduler
+        if (!SPLIT) {
+            if (!(WXB_SW_SKIP & 1)) faces(k, false);
+            if (WXB_SW_ALIAS) __syncthreads();  // the flux fields overwrite rows the face pass reads
+        }
         double* const col = sbuf + LY::fl(k) + le * P + node;
 
         // ---- nodes: forcing and the flux fields of the three directions -> own column of fl ----------------
         double sg = 1.0, p = 1.0, gfac = 0.0, fo[3] = {0.0, 0.0, 0.0};
         const long long qo = qoff0 + (long long)k * lvl;
+        auto nodes = [&]() {
         if (active && !(WXB_SW_SKIP & 2)) {
             const long long e = e0 + (long long)k * ny * nx;
             const double* const mrow = a.chris + e * (35 * P) + node;  // [35][P]: Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta
@@ -640,6 +654,14 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
             }
             col[18 * RS] = lg;
             col[19 * RS] = sg * rho;
+        }
+        };
+        if (SPLIT) {
+            if (node_first) nodes();
+            if (!(WXB_SW_SKIP & 1)) faces(k, false);
+            if (!node_first) nodes();
+        } else {
+            nodes();
         }
         __syncthreads();
         // the next step's rows (own level k+2, halo level k+1): requested now, used after the assemble phase
@@ -760,17 +782,16 @@ __global__ void __launch_bounds__(N* N* N) euler_edge_traces(const EvalArgs a) {
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) x[v] += a.eps * dv[v];
     }
-    srow[0][node] = x[1];
-    srow[1][node] = x[2];
-    srow[2][node] = x[3];
-    srow[R_LRHO][node] = wxbfm::fast_log(x[0], s_tab);
-    srow[R_LRT][node] = wxbfm::fast_log(x[4], s_tab);
+    const int sn = swz_node<N>(node);
+    srow[0][sn] = x[1];
+    srow[1][sn] = x[2];
+    srow[2][sn] = x[3];
+    srow[R_LRHO][sn] = wxbfm::fast_log(x[0], s_tab);
+    srow[R_LRT][sn] = wxbfm::fast_log(x[4], s_tab);
     __syncthreads();
     if (node < F) {
-        int base, step;
-        line_of<N>(f >> 1, node, base, step);
         double o6[NTR];
-        form_trace<N>(&srow[0][0], P, s_ext + (f & 1) * N, base, step, s_tab + WXB_EXPTAB_OFF, o6);
+        form_trace<N>(&srow[0][0], P, s_ext + (f & 1) * N, f >> 1, node, s_tab + WXB_EXPTAB_OFF, o6);
         double* dst = a.sendbuf + (((long long)rec * a.nz + k) * NTR) * F + node;
 #pragma unroll
         for (int v = 0; v < NTR; ++v) dst[v * F] = o6[v];

@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
 #include <new>
 #include <vector>
 
@@ -13,6 +14,7 @@
 namespace {
 
 char g_create_err[512] = "";
+void comm_free(wxb_handle* h);
 
 void set_err(wxb_handle* h, const char* fmt, ...) {
     char* dst = h ? h->err : g_create_err;
@@ -509,6 +511,7 @@ int wxb_destroy(wxb_handle* h) {
     for (int r = 0; r < WXB_TIMING_RING; ++r)
         for (int i = 0; i < 3; ++i)
             if (h->ev_ring[r][i]) cudaEventDestroy(h->ev_ring[r][i]);
+    comm_free(h);
     if (h->pipe_ready) {
         for (int c = 0; c < h->nchunk; ++c) {
             cudaEventDestroy(h->ev_in[c]);
@@ -586,6 +589,196 @@ int wxb_jvp(wxb_handle* h, const double* q, const double* v, const double* rhs0,
     if (r != WXB_OK) return r;
     h->traces_done = false;
     return do_finish(h, q, v, rhs0, dt, eps, mode, 0, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+
+// ---- halo exchange inside the library -------------------------------------------------------------------------
+// NCCL is reached through dlopen (the copy the process has already loaded, e.g. torch's, else the system one): the
+// library carries no link-time dependency on it and single-GPU users never touch it.
+struct WxbNcclId {
+    char internal[WXB_NCCL_ID_BYTES];
+};
+namespace {
+struct NcclApi {
+    void* lib;
+    int (*GetUniqueId)(void*);
+    int (*CommInitRank)(void**, int, WxbNcclId, int);
+    int (*CommDestroy)(void*);
+    int (*GroupStart)();
+    int (*GroupEnd)();
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t);
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t);
+    const char* (*GetErrorString)(int);
+};
+NcclApi g_nccl = {};
+
+int load_nccl(wxb_handle* h) {
+    if (g_nccl.lib) return WXB_OK;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) {
+        set_err(h, "cannot load libnccl.so.2: %s", dlerror());
+        return WXB_ECUDA;
+    }
+    NcclApi a = {};
+    a.lib = lib;
+    *(void**)&a.GetUniqueId = dlsym(lib, "ncclGetUniqueId");
+    *(void**)&a.CommInitRank = dlsym(lib, "ncclCommInitRank");
+    *(void**)&a.CommDestroy = dlsym(lib, "ncclCommDestroy");
+    *(void**)&a.GroupStart = dlsym(lib, "ncclGroupStart");
+    *(void**)&a.GroupEnd = dlsym(lib, "ncclGroupEnd");
+    *(void**)&a.Send = dlsym(lib, "ncclSend");
+    *(void**)&a.Recv = dlsym(lib, "ncclRecv");
+    *(void**)&a.GetErrorString = dlsym(lib, "ncclGetErrorString");
+    if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.GroupStart || !a.GroupEnd || !a.Send || !a.Recv) {
+        set_err(h, "libnccl.so.2 lacks a required symbol");
+        return WXB_ECUDA;
+    }
+    g_nccl = a;
+    return WXB_OK;
+}
+
+#define NC(call)                                                                                                   \
+    do {                                                                                                           \
+        int _e = (call);                                                                                           \
+        if (_e != 0) {                                                                                             \
+            set_err(h, "%s failed: %s", #call, g_nccl.GetErrorString ? g_nccl.GetErrorString(_e) : "NCCL error"); \
+            return WXB_ECUDA;                                                                                      \
+        }                                                                                                          \
+    } while (0)
+
+void comm_free(wxb_handle* h) {
+    if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
+    h->nccl_comm = nullptr;
+    if (h->s_comm) cudaStreamDestroy(h->s_comm);
+    if (h->ev_packed) cudaEventDestroy(h->ev_packed);
+    if (h->ev_halo) cudaEventDestroy(h->ev_halo);
+    h->s_comm = nullptr;
+    h->ev_packed = h->ev_halo = nullptr;
+    for (int** p : {&h->send_peer, &h->send_first, &h->send_count, &h->recv_peer, &h->recv_first, &h->recv_count}) {
+        free(*p);
+        *p = nullptr;
+    }
+}
+
+int copy_list(int** dst, const int32_t* src, int n) {
+    *dst = (int*)malloc(sizeof(int) * (n > 0 ? n : 1));
+    if (!*dst) return WXB_ENOMEM;
+    for (int i = 0; i < n; ++i) (*dst)[i] = src[i];
+    return WXB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int wxb_comm_unique_id(void* id_out) {
+    wxb_handle* h = nullptr;
+    if (!id_out) return WXB_EINVAL;
+    int r = load_nccl(h);
+    if (r != WXB_OK) return r;
+    NC(g_nccl.GetUniqueId(id_out));
+    return WXB_OK;
+}
+
+int wxb_comm_init(wxb_handle* h, const void* id, int rank, int nranks, int n_send_peers, const int32_t* send_peer,
+                  const int32_t* send_first, const int32_t* send_count, int n_recv_peers, const int32_t* recv_peer,
+                  const int32_t* recv_first, const int32_t* recv_count) {
+    if (!h) return WXB_EINVAL;
+    if (!id || rank < 0 || rank >= nranks || n_send_peers < 0 || n_recv_peers < 0) {
+        set_err(h, "bad communicator arguments (rank %d of %d)", rank, nranks);
+        return WXB_EINVAL;
+    }
+    long long ns = 0, nr = 0;
+    for (int i = 0; i < n_send_peers; ++i) {
+        if (send_peer[i] < 0 || send_peer[i] >= nranks || send_peer[i] == rank || send_first[i] != ns || send_count[i] <= 0) {
+            set_err(h, "send list entry %d is not a contiguous slice of the send buffer for another rank", i);
+            return WXB_EINVAL;
+        }
+        ns += send_count[i];
+    }
+    for (int i = 0; i < n_recv_peers; ++i) {
+        if (recv_peer[i] < 0 || recv_peer[i] >= nranks || recv_peer[i] == rank || recv_first[i] != nr || recv_count[i] <= 0) {
+            set_err(h, "receive list entry %d is not a contiguous slice of the ghost records from another rank", i);
+            return WXB_EINVAL;
+        }
+        nr += recv_count[i];
+    }
+    if (ns != h->cfg.nsend || nr != h->cfg.nghost) {
+        set_err(h, "peer lists cover %lld send / %lld ghost records, the handle has %d / %d", ns, nr, h->cfg.nsend, h->cfg.nghost);
+        return WXB_EINVAL;
+    }
+    int r = load_nccl(h);
+    if (r != WXB_OK) return r;
+    CU(cudaSetDevice(h->device));
+    comm_free(h);
+    WxbNcclId uid;
+    memcpy(uid.internal, id, WXB_NCCL_ID_BYTES);
+    NC(g_nccl.CommInitRank(&h->nccl_comm, nranks, uid, rank));
+    CU(cudaStreamCreateWithFlags(&h->s_comm, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_packed, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
+    h->comm_rank = rank;
+    h->comm_nranks = nranks;
+    h->n_send_peers = n_send_peers;
+    h->n_recv_peers = n_recv_peers;
+    if ((r = copy_list(&h->send_peer, send_peer, n_send_peers)) || (r = copy_list(&h->send_first, send_first, n_send_peers)) ||
+        (r = copy_list(&h->send_count, send_count, n_send_peers)) || (r = copy_list(&h->recv_peer, recv_peer, n_recv_peers)) ||
+        (r = copy_list(&h->recv_first, recv_first, n_recv_peers)) || (r = copy_list(&h->recv_count, recv_count, n_recv_peers)))
+        return r;
+    return WXB_OK;
+}
+
+int wxb_exchange(wxb_handle* h, void* stream) {
+    if (!h) return WXB_EINVAL;
+    if (!h->nccl_comm) {
+        set_err(h, "wxb_exchange before wxb_comm_init");
+        return WXB_ESTATE;
+    }
+    CU(cudaSetDevice(h->device));
+    const size_t rec = (size_t)h->ntr * (h->cfg.equations == WXB_EQ_EULER3D ? h->cfg.nz : 1) * h->F;  // doubles per record
+    double* recv = h->d_trace + h->trace_local;
+    NC(g_nccl.GroupStart());
+    for (int i = 0; i < h->n_send_peers; ++i)
+        NC(g_nccl.Send(h->d_sendbuf + (size_t)h->send_first[i] * rec, (size_t)h->send_count[i] * rec, 8 /* ncclFloat64 */, h->send_peer[i],
+                       h->nccl_comm, (cudaStream_t)stream));
+    for (int i = 0; i < h->n_recv_peers; ++i)
+        NC(g_nccl.Recv(recv + (size_t)h->recv_first[i] * rec, (size_t)h->recv_count[i] * rec, 8, h->recv_peer[i], h->nccl_comm, (cudaStream_t)stream));
+    NC(g_nccl.GroupEnd());
+    return WXB_OK;
+}
+
+// One whole evaluation on a handle WITH remote neighbours: boundary traces -> exchange on the handle's communication
+// stream, overlapped with the tiles / elements that read no ghost record -> the rest.  mode -1 = plain RHS.
+int wxb_eval_dist(wxb_handle* h, const double* q, const double* v, const double* rhs0, double dt, double eps, int mode, double* out,
+                  void* stream) {
+    if (!h) return WXB_EINVAL;
+    int r = check_mode(h, q, mode >= 0 ? v : nullptr, mode >= 0 ? rhs0 : nullptr, eps, mode, out);
+    if (r != WXB_OK) return r;
+    if (h->cfg.nghost != 0 && !h->nccl_comm) {
+        set_err(h, "handle has remote neighbours: call wxb_comm_init first (or use wxb_traces / your own exchange / wxb_finish)");
+        return WXB_ESTATE;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const double* vv = mode >= 0 ? v : nullptr;
+    r = do_traces(h, q, vv, eps, s);
+    if (r != WXB_OK) return r;
+    if (h->cfg.nghost != 0) {
+        CU(cudaEventRecord(h->ev_packed, s));
+        CU(cudaStreamWaitEvent(h->s_comm, h->ev_packed, 0));
+        r = wxb_exchange(h, h->s_comm);
+        if (r != WXB_OK) return r;
+        CU(cudaEventRecord(h->ev_halo, h->s_comm));
+        r = do_finish(h, q, vv, rhs0, dt, eps, mode, 1, out, s);
+        if (r != WXB_OK) return r;
+        CU(cudaStreamWaitEvent(s, h->ev_halo, 0));
+        r = do_finish(h, q, vv, rhs0, dt, eps, mode, 2, out, s);
+    } else {
+        r = do_finish(h, q, vv, rhs0, dt, eps, mode, 0, out, s);
+    }
+    h->traces_done = false;
+    return r;
 }
 
 static int host_stage(wxb_handle* h) {

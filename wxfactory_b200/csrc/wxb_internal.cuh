@@ -111,6 +111,13 @@ struct wxb_handle {
     long long nevals;     // completed evaluations
     bool timed;
     bool traces_done;
+    // halo exchange inside the library (wxb_comm_init / wxb_exchange): NCCL point-to-point on the handle's own stream
+    void* nccl_comm;
+    cudaStream_t s_comm;
+    cudaEvent_t ev_packed, ev_halo;
+    int comm_rank, comm_nranks;
+    int n_send_peers, n_recv_peers;
+    int *send_peer, *send_first, *send_count, *recv_peer, *recv_first, *recv_count;  // host arrays
     char err[512];
 };
 

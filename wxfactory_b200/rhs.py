@@ -107,6 +107,11 @@ class RhsB200:
         self._torch = None
         self._send_t = self._recv_t = None
         self._comm_stream = None
+        # multi-rank handles: the halo exchange runs inside the library (wxb_comm_init / wxb_eval_dist: NCCL send / recv on
+        # the handle's own stream).  WXB_HALO=torch keeps the torch.distributed point-to-point exchange of halo.py.
+        self._lib_comm = False
+        if self.nranks > 1 and os.environ.get("WXB_HALO", "lib") != "torch":
+            self._init_lib_comm()
 
     # ---- lifetime ---------------------------------------------------------------------------------
     def close(self):
@@ -186,8 +191,8 @@ class RhsB200:
     def _to_host(self, t):
         """Device result -> numpy (through a reusable pinned buffer; synchronises)."""
         torch = self._tm()
-        out = torch.empty(t.numel(), dtype=torch.float64, pin_memory=True)
-        out.copy_(t.view(-1), non_blocking=True)
+        out = torch.empty(t.numel(), dtype=torch.float64, pin_memory=True)  # torch's caching host allocator: a page-locked
+        out.copy_(t.view(-1), non_blocking=True)                           # block is re-used once its last owner let go
         torch.cuda.current_stream(t.device).synchronize()
         return out.numpy()
 
@@ -202,7 +207,35 @@ class RhsB200:
             self._check(k, "wxb_timing_history")
         return numpy.array(ms[: 3 * k], dtype=numpy.float64).reshape(k, 3), numpy.array(md[:k], dtype=numpy.int64)
 
-    # ---- halo exchange between ranks (NCCL through torch.distributed) -------------------------------
+    # ---- halo exchange between ranks ---------------------------------------------------------------------
+    def _init_lib_comm(self):
+        """Join the library's own NCCL communicator: rank 0 makes the unique id, torch.distributed ships it."""
+        import torch.distributed as dist
+
+        torch = self._tm()
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_backend(self.group) != "nccl":
+            return  # CPU / gloo jobs (tests) keep the torch exchange
+        idbuf = (ctypes.c_char * capi.WXB_NCCL_ID_BYTES)()
+        if self.rank == 0:
+            self._check(self._lib.wxb_comm_unique_id(ctypes.byref(idbuf)), "wxb_comm_unique_id")
+        box = [bytes(idbuf.raw)]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        idbuf.raw = box[0]
+
+        def lists(peers):
+            arr = numpy.asarray(peers, dtype=numpy.int32).reshape(-1, 3)
+            return len(peers), [numpy.ascontiguousarray(arr[:, c]) for c in range(3)]
+
+        ns, (sp, sf, sc) = lists(self.part.send_peers)
+        nr, (rp, rf, rc) = lists(self.part.recv_peers)
+        torch.cuda.set_device(self.device_index)
+        self._check(
+            self._lib.wxb_comm_init(self._h, ctypes.byref(idbuf), self.rank, self.nranks, ns, sp.ctypes.data, sf.ctypes.data, sc.ctypes.data,
+                                    nr, rp.ctypes.data, rf.ctypes.data, rc.ctypes.data),
+            "wxb_comm_init",
+        )
+        self._lib_comm = True
+
     def _exchange(self, stream):
         torch = self._tm()
         if self._send_t is None:
@@ -229,6 +262,8 @@ class RhsB200:
                 self._check(self._lib.wxb_rhs(self._h, q.data_ptr(), out.data_ptr(), sp), "wxb_rhs")
             else:
                 self._check(self._lib.wxb_jvp(self._h, q.data_ptr(), vp, rp, dt, eps, mode, out.data_ptr(), sp), "wxb_jvp")
+        elif self._lib_comm:
+            self._check(self._lib.wxb_eval_dist(self._h, q.data_ptr(), vp, rp, dt, eps, mode, out.data_ptr(), sp), "wxb_eval_dist")
         else:
             if self._comm_stream is None:
                 self._comm_stream = torch.cuda.Stream(device=q.device)
@@ -311,6 +346,16 @@ class RhsB200:
             self.timestamps = [True]
             self._lin_token = getattr(self, "_lin_token", 0) + 1
             return MatvecOpB200(self, dt, Q, out.reshape(Q.shape), mode, eps, token=self._lin_token)
+        if isinstance(Q, numpy.ndarray):
+            # multi-rank handle, host arrays: Q goes up once, RHS(Q) comes down once and BOTH stay on the device with the
+            # operator, so that every application moves only vec up and the product down (2 uploads per step, not 4)
+            torch = self._tm()
+            qd = torch.from_numpy(self._as_host(Q, "Q").reshape(-1)).to(f"cuda:{self.device_index}", non_blocking=True)
+            rd = self._eval_device(qd, None, None, 0.0, 0.0, -1)
+            self.timestamps = [True]
+            op = MatvecOpB200(self, dt, Q, self._to_host(rd).reshape(Q.shape), mode, eps, token=None)
+            op._dev = (qd, rd)
+            return op
         return MatvecOpB200(self, dt, Q, self(Q), mode, eps, token=None)
 
     def _bind(self, Q, rhs0):
@@ -388,8 +433,15 @@ class MatvecOpB200:
     def matvec(self, vec):
         return self(vec)
 
+    _dev = None  # (Q, RHS(Q)) kept on the device by RhsB200.linearize on a multi-rank handle
+
     def __call__(self, vec):
         o = self.owner
+        if self._dev is not None and isinstance(vec, numpy.ndarray):
+            torch = o._tm()
+            vd = torch.from_numpy(o._as_host(vec, "vec").reshape(-1)).to(self._dev[0].device, non_blocking=True)
+            m = capi.JVP_FD if self.mode == "fd" else capi.JVP_RAT
+            return o._to_host(o._eval_device(self._dev[0], vd, self._dev[1], float(self.dt), float(self.eps), m))
         if not (self._host and isinstance(vec, numpy.ndarray)):
             return o.jvp(vec, self.dt, self.Q, self.rhs, mode=self.mode, eps=self.eps)
         if self._token is None or self._token != getattr(o, "_lin_token", 0):
