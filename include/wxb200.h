@@ -236,6 +236,18 @@ int64_t wxb_vec_multidot_scratch(int m, int k);
 int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
                      double* scratch_dev, void* stream);
 
+/* wxb_vec_multidot for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs,
+ * outputs and arithmetic as wxb_vec_multidot, but the scratch of the two-stage reduction lives in a file-scope device
+ * array inside the library (592 KiB on every GPU that loads it), so the caller passes none and the call performs no
+ * cudaMalloc / cudaFree / allocating library call.  Limit: m <= WXB_VEC_STATIC_MAX_ROWS (WXB_EINVAL beyond it; use
+ * wxb_vec_multidot with caller scratch there).  All calls on a device share the one array: calls that overlap on the GPU
+ * (different streams, no ordering between them) RACE -- order them.  Nothing needs clearing between calls: every partial
+ * sum the second stage reads is rewritten by the first stage of the same call. */
+#define WXB_VEC_STATIC_MAX_ROWS 64
+int wxb_vec_multidot_static(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
+                            void* stream);
+
 /* Scalar reductions (fixed order; scratch_dev as for wxb_vec_multidot(1, 1)):
  *   kind 0: *out_dev = sum_i |x[i]|                  <- 1-norms of the phi vectors, kiops.py:111-116, pmex.py:91-98
  *   kind 1: *out_dev = max_{x[i] != 0} |y[i] / x[i]|, -1 if x == 0   <- stagnation test update/x of fgmres.py:257-262 */

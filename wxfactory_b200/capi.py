@@ -97,6 +97,7 @@ EXPORTS = [
     "wxb_vec_nonfinite",
     "wxb_vec_multidot_scratch",
     "wxb_vec_multidot",
+    "wxb_vec_multidot_static",
     "wxb_vec_reduce",
     "wxb_vec_combine",
     "wxb_vec_gs1sync",
@@ -151,6 +152,7 @@ def load():
     lib.wxb_vec_multidot_scratch.argtypes = [i32, i32]
     lib.wxb_vec_multidot_scratch.restype = i64
     lib.wxb_vec_multidot.argtypes = [i64, i32, vp, i64, i32, vp, i64, vp, vp, vp]
+    lib.wxb_vec_multidot_static.argtypes = [i64, i32, vp, i64, i32, vp, i64, vp, vp]
     lib.wxb_vec_reduce.argtypes = [i64, i32, vp, vp, vp, vp, vp]
     lib.wxb_vec_combine.argtypes = [i64, i32, vp, vp, i64, dbl, vp, dbl, vp, vp]
     lib.wxb_vec_gs1sync.argtypes = [i64, i32, vp, vp, vp, i64, dbl, dbl, vp, vp, vp]

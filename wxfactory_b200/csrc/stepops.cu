@@ -401,6 +401,31 @@ int wxb_vec_multidot(int64_t n, int m, const double* V, int64_t ldv, int k, cons
     return cudaGetLastError() == cudaSuccess ? WXB_OK : WXB_ECUDA;
 }
 
+// ---- wxb_vec_multidot without any allocation -------------------------------------------------------------------
+// Scratch of the two-stage reduction in a file-scope device array (every GPU that loads the library holds these
+// WXB_VEC_STATIC_SCRATCH_DOUBLES * 8 bytes = 592 KiB until exit).  In host code `g_md_scratch` is only a stand-in for
+// the symbol: the kernels get its device address, resolved once per device with cudaGetSymbolAddress.
+#define WXB_VEC_STATIC_SCRATCH_DOUBLES (VEC_BLOCKS * WXB_VEC_STATIC_MAX_ROWS * 2)
+static __device__ __align__(256) double g_md_scratch[WXB_VEC_STATIC_SCRATCH_DOUBLES];
+static double* g_md_scratch_addr[64];  // per device ordinal, filled at the first call on that device
+
+int wxb_vec_multidot_static(int64_t n, int m, const double* V, int64_t ldv, int k, const double* W, int64_t ldw, double* out_dev,
+                            void* stream) {
+    if (m > WXB_VEC_STATIC_MAX_ROWS) return WXB_EINVAL;  // beyond the static scratch: use wxb_vec_multidot with caller scratch
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return WXB_ECUDA;
+    if (!g_md_scratch_addr[dev]) {  // set-up, once per device, with that device current
+        double* ptr = nullptr;
+        if (cudaGetSymbolAddress((void**)&ptr, g_md_scratch) != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            return WXB_ECUDA;
+        }
+        g_md_scratch_addr[dev] = ptr;
+    }
+    // every partial sum the final stage reads is written by this call's first stage: nothing has to start at zero
+    return wxb_vec_multidot(n, m, V, ldv, k, W, ldw, out_dev, g_md_scratch_addr[dev], stream);
+}
+
 int wxb_vec_reduce(int64_t n, int kind, const double* x, const double* y, double* out_dev, double* scratch_dev, void* stream) {
     if (n <= 0 || (kind != 0 && kind != 1) || !x || (kind == 1 && !y) || !out_dev || !scratch_dev) return WXB_EINVAL;
     cudaStream_t s = (cudaStream_t)stream;
