@@ -358,7 +358,7 @@ def run_b200(args):
     total_nodes = tiled.num_nodes
     total_dofs = tiled.num_dofs
     state_bytes = size * 8
-    path_name = "sweep" if rhs.sweep else "split"
+    path_name = rhs.path_name
 
     # ---- full-size parity through the tiling periodicity property (untimed) ---------------------------------
     small_ref = None
@@ -447,7 +447,7 @@ def run_b200(args):
 
     peak, peak_src = measured_peaks()
     traffic, traffic_src = ncu_traffic(path_name) if n == 4 else (None, "captured at n = 4 only")
-    kernels = ["euler_sweep<4>"] if rhs.sweep else ["euler_traces<4>", "euler_main<4>"]
+    kernels = {k: (["euler_sweep<4>"] if rhs._fused[i] else ["euler_traces<4>", "euler_main<4>"]) for i, k in enumerate(("rhs", "jvp"))}
     line = None
     if rank == 0:
         def roof(tt, bytes_per_node, what, key, sus_ms):
@@ -463,7 +463,7 @@ def run_b200(args):
                 "frac": ach / peak,
                 "traffic": traffic[key] * nodes_local if traffic else None,
                 "traffic_source": traffic_src,
-                "kernels": kernels,
+                "kernels": kernels[key],
                 "launch_ms": {"traces": _median(tt[:, 0]), "main": _median(tt[:, 1]), "evaluation": ev_ms},
                 "algorithmic_bytes_per_node": bytes_per_node,
                 "nodes_per_launch": nodes_local,
@@ -714,7 +714,7 @@ def run_shallow_water(args):
         sec = float(tt[:, 2].mean()) * 1e-3
         ach = bpn * nodes / sec / 1e9
         return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                "kernels": [f"sw_traces<{n}>", f"sw_main<{n}>"],
+                "kernels": [f"sw_tile<{n}>"] if rhs._fused[0] else [f"sw_traces<{n}>", f"sw_main<{n}>"],
                 "launch_ms": {"traces": float(tt[:, 0].mean()), "main": float(tt[:, 1].mean()), "evaluation": float(tt[:, 2].mean())},
                 "algorithmic_bytes_per_node": bpn, "nodes_per_launch": nodes, "launches_timed": int(len(tt)), "what": what}
 

@@ -89,7 +89,9 @@ class OracleRhsB200(rhs_mod.RhsB200):
         self.prob, self.nranks, self.rank, self.device_index, self.group = problem, 1, 0, device, process_group
         euler = problem.equations == "euler"
         self.num_var = problem.num_var
-        self.sweep = euler
+        self.sweep = True
+        self._fused = (True, True)
+        self.path_name = "sweep" if euler else "tile"
         self.num_trace = 6 if euler else 3
         self.part = build_partition(problem.nh, problem.nz if euler else 1, problem.n, problem.bnd_sn, problem.bnd_we, num_var=self.num_trace,
                                     nfaces=6 if euler else 4, trace_layout="element" if euler else "field")

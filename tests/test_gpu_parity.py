@@ -214,18 +214,19 @@ def test_timings_vocabulary(rhs_cache):
     assert len(rhs.timings) >= 1 and all(t[2] > 0 for t in rhs.timings)
 
 
-def test_split_path_matches_too():
-    """The Euler handles run the fused column-sweep kernel (csrc/euler_sweep.cu) by default; the traces + main pair of
-    csrc/euler3d.cu is selected per process with WXB_EULER_PATH=split: run the device-path parity cases again in a
-    child process with it switched on."""
+@pytest.mark.parametrize("env", [{"WXB_EULER_PATH": "split", "WXB_SW_PATH": "split"}])
+def test_other_kernel_paths_match_too(env):
+    """By default an Euler handle runs the fused column-sweep kernel (csrc/euler_sweep.cu) and a shallow-water handle the
+    fused tile kernel (csrc/sw_tile.cu).  WXB_EULER_PATH = split / WXB_SW_PATH = split select the traces + main pairs
+    (csrc/euler3d.cu, csrc/sw2d.cu) per process: run the device-path, JVP and host-pipeline parity cases again in a
+    child process with them."""
     import subprocess
     import sys
 
-    env = dict(os.environ, WXB_EULER_PATH="split")
     here = os.path.abspath(__file__)
     r = subprocess.run(
-        [sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k", "device_path or jvp_matches"],
-        env=env, capture_output=True, text=True, timeout=600,
+        [sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k", "device_path or jvp_matches or host_pipeline"],
+        env=dict(os.environ, **env), capture_output=True, text=True, timeout=600,
     )
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 

@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libwxb200.so")
-SOURCES = ["wxb_api.cu", "euler3d.cu", "euler_sweep.cu", "sw2d.cu", "stepops.cu"]
+SOURCES = ["wxb_api.cu", "euler3d.cu", "euler_sweep.cu", "sw2d.cu", "sw_tile.cu", "stepops.cu"]
 NVCC_FLAGS = [
     "-gencode",
     "arch=compute_100a,code=sm_100a",

@@ -115,7 +115,7 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.build_if_stale()
+    path = os.environ.get("WXB_LIB_PATH") or _build.build_if_stale()  # WXB_LIB_PATH: an alternative build (A/B runs)
     lib = ctypes.CDLL(path)
     vp, i32, i64, dbl = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
     lib.wxb_version.restype = i32

@@ -67,7 +67,8 @@
 #define WXB_RCP 1  // velocities through one reciprocal of rho per point instead of three divisions
 #endif
 #ifndef WXB_FASTMATH
-#define WXB_FASTMATH 1  // table-driven branch-free exp / log / reciprocal / sqrt of fastmath.cuh (tables read through L1)
+#define WXB_FASTMATH 0  // 1: table-driven exp / log / reciprocal / sqrt of fastmath.cuh; here the tables are read through L1 from
+                        // global memory and that costs 2-3 % (A/B on B200, profiles/r02_libs_ab.log): off on this path
 #endif
 
 // Formulation knobs of the trace / interface path (A/B'd on B200: profiles/r01_trace_variants.log):

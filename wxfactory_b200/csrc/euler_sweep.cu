@@ -86,6 +86,10 @@
                              // the node pass waits for 40 loads per thread, the face pass is arithmetic on shared memory, so
                              // each half's loads fly while the other half computes (needs WXB_SW_ALIAS = 0)
 #endif
+#ifndef WXB_SW_JVP_EARLY_OWN
+#define WXB_SW_JVP_EARLY_OWN 0  // 1: JVP mode requests the own rows (q and v) of the next level ahead of the assemble phase too
+                                // (measured slower: JVP 1.41 vs 1.37 ms, the 20 registers held cost more than the latency hidden)
+#endif
 #ifndef WXB_SW_CH3
 #define WXB_SW_CH3 0  // 1: Christoffel symbols loaded 9 at a time where they are used (fewer registers, less memory parallelism)
 #endif
@@ -142,6 +146,14 @@ struct FaceDesc {
 };
 
 constexpr int R_M = 0, R_LRHO = 3, R_LRT = 4, NSTAGE = 5;  // staged rows: rho u1, rho u2, rho w, log rho, log(rho theta)
+// own elements also keep rho and rho theta (of q, or of q + eps v): the node pass of the level then reads its state from
+// shared memory instead of loading q (and v) a second time (not with WXB_SW_ALIAS, where the flux fields overwrite the rows)
+// (n = 5: the two extra rows would push the block over half an SM's shared memory)
+template <int N>
+struct QSmem {
+    static constexpr bool value = !WXB_SW_ALIAS && N != 5;
+};
+constexpr int R_RHO = 5, R_RT = 6;
 constexpr int NFLUX = 20;  // per direction F_rho F_u1 F_u2 F_theta w_adv w_pres; then log(Rd/p0 rho theta), sqrtG rho
 
 // staged rows and flux fields in one array (doubles):
@@ -153,7 +165,7 @@ constexpr int NFLUX = 20;  // per direction F_rho F_u1 F_u2 F_theta w_adv w_pres
 template <int N>
 struct SweepLayout {
     using C = SCfg<N>;
-    static constexpr int SO = NSTAGE * C::NE * C::P, SH = NSTAGE * C::NH * C::P, FL = NFLUX * C::NE * C::P;
+    static constexpr int SO = (QSmem<N>::value ? 7 : 5) * C::NE * C::P, SH = NSTAGE * C::NH * C::P, FL = NFLUX * C::NE * C::P;
     static constexpr int PAD = FL > SO + SH ? FL - SO - SH : 0;
     static constexpr int TOTAL = WXB_SW_ALIAS ? 2 * SO + SH + PAD : 2 * SO + SH + FL;
     __device__ static constexpr int so(int b) { return WXB_SW_ALIAS ? (b ? SO + SH + PAD : 0) : b * SO; }
@@ -391,7 +403,8 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
     constexpr int HR = (NH * P + NT - 1) / NT;
     // JVP mode stages q + eps*v: twice the operands to hold, so there the rows are requested where they are used
     // (register budget: 128 at two resident blocks)
-    constexpr bool EARLY = !JVP && HR <= 2;
+    constexpr bool EARLY = !JVP && HR <= 2;      // halo rows requested early
+    constexpr bool EARLY_OWN = WXB_SW_JVP_EARLY_OWN ? HR <= 2 : EARLY;  // own rows requested early
     double xo[NVAR], xh[HR][NVAR];
     double vo[JVP ? NVAR : 1], vh[HR][JVP ? NVAR : 1];
     auto halo_load1 = [&](int kh, int r) {
@@ -425,15 +438,17 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
         }
     };
     auto stage_load = [&](int ko, int kh) {
-        if (EARLY) {
-            own_load(ko);
-            if (kh >= 0) halo_load(kh);
-        }
+        if (EARLY_OWN) own_load(ko);
+        if (EARLY && kh >= 0) halo_load(kh);
     };
-    auto stage_put = [&](double* dst, int rs, double x[NVAR], const double* dv) {
+    auto stage_put = [&](double* dst, int rs, double x[NVAR], const double* dv, bool own) {
         if (JVP) {
 #pragma unroll
             for (int v = 0; v < NVAR; ++v) x[v] += a.eps * dv[v];
+        }
+        if (QSmem<N>::value && own) {
+            dst[R_RHO * rs] = x[0];
+            dst[R_RT * rs] = x[4];
         }
         dst[0] = x[1];
         dst[rs] = x[2];
@@ -442,15 +457,15 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
         dst[R_LRT * rs] = wxbfm::fast_log(x[4], ltab);
     };
     auto stage_store = [&](int ko, int kh) {
-        if (!EARLY) own_load(ko);
-        if (active && ko >= 0) stage_put(sbuf + LY::so(ko & 1) + le * P + swz_node<N>(node), RSO, xo, vo);
+        if (!EARLY_OWN) own_load(ko);
+        if (active && ko >= 0) stage_put(sbuf + LY::so(ko & 1) + le * P + swz_node<N>(node), RSO, xo, vo, true);
         if (kh >= 0) {
 #pragma unroll
             for (int r = 0; r < HR; ++r) {
                 if (!EARLY) halo_load1(kh, r);
                 const int t = tid + r * NT;
                 const int h = t / P, hn = t - h * P;
-                if (t < NH * P && sm.hd[h].kind == 1 && !(WXB_SW_SKIP & 8)) stage_put(sbuf + LY::sh() + h * P + swz_node<N>(hn), RSH, xh[r], vh[r]);
+                if (t < NH * P && sm.hd[h].kind == 1 && !(WXB_SW_SKIP & 8)) stage_put(sbuf + LY::sh() + h * P + swz_node<N>(hn), RSH, xh[r], vh[r], false);
             }
         }
     };
@@ -597,14 +612,23 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
             const long long e = e0 + (long long)k * ny * nx;
             const double* const mrow = a.chris + e * (35 * P) + node;  // [35][P]: Christoffel 0..26 | sqrtG | h 0..5 | 1/z_eta
             double q[NVAR], h[6], ch[WXB_SW_CH3 ? 1 : 27];
+            if (QSmem<N>::value) {  // staged one step ahead (q, or q + eps v)
+                const double* sq = sbuf + LY::so(k & 1) + le * P + swz_node<N>(node);
+                q[0] = sq[R_RHO * RSO];
+                q[1] = sq[0];
+                q[2] = sq[RSO];
+                q[3] = sq[2 * RSO];
+                q[4] = sq[R_RT * RSO];
+            } else {
 #pragma unroll
-            for (int v = 0; v < NVAR; ++v) q[v] = a.q[qo + v * vstride];
-            if (JVP) {
-                double dv[NVAR];
+                for (int v = 0; v < NVAR; ++v) q[v] = a.q[qo + v * vstride];
+                if (JVP) {
+                    double dv[NVAR];
 #pragma unroll
-                for (int v = 0; v < NVAR; ++v) dv[v] = a.v[qo + v * vstride];
+                    for (int v = 0; v < NVAR; ++v) dv[v] = a.v[qo + v * vstride];
 #pragma unroll
-                for (int v = 0; v < NVAR; ++v) q[v] += a.eps * dv[v];
+                    for (int v = 0; v < NVAR; ++v) q[v] += a.eps * dv[v];
+                }
             }
             sg = mrow[27 * P];
 #pragma unroll

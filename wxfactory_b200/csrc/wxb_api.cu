@@ -220,11 +220,15 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     UP(h->d_xform, A->xform, (size_t)cfg->nxform * n * 4);
     UP(h->d_send, A->send, (size_t)cfg->nsend);
 
-    // Euler: the column-sweep path (euler_sweep.cu, default) or the two-kernel path of euler3d.cu (WXB_EULER_PATH=split)
-    h->sweep = false;
-    if (euler) {
-        const char* pe = getenv("WXB_EULER_PATH");
-        h->sweep = !(pe && strcmp(pe, "split") == 0);
+    // Which kernels serve the handle: the fused kernel (Euler: euler_sweep.cu, WXB_EULER_PATH=sweep, default; shallow water:
+    // sw_tile.cu, WXB_SW_PATH=tile, default) or the traces + main pair (euler3d.cu / sw2d.cu, "split").  One path serves
+    // BOTH operators of a handle: the FD Jacobian-vector product subtracts the cached RHS(Q) from RHS(Q + eps v), and the
+    // rounding of the two evaluations only cancels (amplified by 1/eps otherwise) when both come from the same kernels --
+    // a mixed mode (RHS fused, JVP pair) was measured faster and broke the Krylov iteration counts of Epi(2) on dcmip31.
+    {
+        const char* pe = getenv(euler ? "WXB_EULER_PATH" : "WXB_SW_PATH");
+        h->split = pe && strcmp(pe, "split") == 0;
+        h->sweep = !h->split;
     }
     // trace array: local part (SW [ntr][nfaces][E][F], Euler [E][nfaces][ntr][F]), then the ghost records
     // (SW [rec][ntr][1][F], Euler [rec][nz][ntr][F]); the same number of doubles either way.  The sweep path has no
@@ -232,10 +236,10 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     h->trace_local = (int64_t)h->ntr * h->nfaces * h->E * h->F;
     const int64_t ghost = (int64_t)cfg->nghost * h->ntr * nz * h->F;
     {
-        const int64_t alloc = (h->sweep ? 0 : h->trace_local) + ghost + 1;
+        const int64_t alloc = (h->split ? h->trace_local : 0) + ghost + 1;
         CU(cudaMalloc((void**)&h->d_trace_alloc, (size_t)alloc * sizeof(double)));
         CU(cudaMemset(h->d_trace_alloc, 0, (size_t)alloc * sizeof(double)));
-        h->d_trace = h->sweep ? h->d_trace_alloc - h->trace_local : h->d_trace_alloc;
+        h->d_trace = h->split ? h->d_trace_alloc : h->d_trace_alloc - h->trace_local;
     }
     if (cfg->nsend > 0) CU(cudaMalloc((void**)&h->d_sendbuf, (size_t)cfg->nsend * h->ntr * nz * h->F * sizeof(double)));
     if (euler) {  // log / exp tables of fastmath.cuh
@@ -246,7 +250,8 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     if (h->sweep) {
         // tiles of TJ x TI columns, slab after slab, row-major; a tile is "outer" if one of its columns reads a ghost
         int tj = 1, ti = 1;
-        wxb_sweep_tile_shape(n, &tj, &ti);
+        if (euler) wxb_sweep_tile_shape(n, &tj, &ti);
+        else wxb_sw_tile_shape(n, &tj, &ti);
         std::vector<int> tin, tout;
         const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
         int tile = 0;
@@ -270,14 +275,14 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
             UP(h->d_tiles_inner, tin.data(), tin.size());
             UP(h->d_tiles_outer, tout.data(), tout.size());
         }
-        if (wxb_sweep_configure(n) != 0) {
+        if (euler && wxb_sweep_configure(n) != 0) {
             set_err(h, "cannot configure the sweep kernel's shared memory: %s", cudaGetErrorString(cudaGetLastError()));
             return WXB_ECUDA;
         }
     }
 
     // inner / outer element lists: an element is "outer" if one of its horizontal faces reads a ghost record
-    if (cfg->nghost > 0 && !h->sweep) {
+    if (cfg->nghost > 0 && h->split) {
         std::vector<int> inner, outer;
         const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
         for (int s = 0; s < cfg->nslabs; ++s) {
@@ -298,12 +303,15 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     for (int r = 0; r < WXB_TIMING_RING; ++r)
         for (int i = 0; i < 3; ++i) CU(cudaEventCreate(&h->ev_ring[r][i]));
     h->ev = h->ev_ring[0];
-    if (euler && !h->sweep && wxb_euler_configure(n) != 0) {
+    if (euler && h->split && wxb_euler_configure(n) != 0) {
         set_err(h, "cannot configure the main kernel's shared memory: %s", cudaGetErrorString(cudaGetLastError()));
         return WXB_ECUDA;
     }
     return WXB_OK;
 }
+
+// the fused kernel or the traces + main pair (one path per handle, see build())
+bool use_fused(const wxb_handle* h, bool /*jvp*/) { return h->sweep; }
 
 void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, const double* rhs0, double dt, double eps,
                int mode, double* out) {
@@ -373,7 +381,9 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
         h->traces_done = true;
         return WXB_OK;
     }
-    if (v && !h->d_qp && !h->sweep) {  // first JVP on this handle: scratch for the perturbed state
+    const bool fused = use_fused(h, v != nullptr);
+    const bool euler_eq = h->cfg.equations == WXB_EQ_EULER3D;
+    if (v && !h->d_qp && !fused) {  // first JVP on this handle: scratch for the perturbed state
         CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     }
     EvalArgs a;
@@ -381,8 +391,8 @@ int do_traces(wxb_handle* h, const double* q, const double* v, double eps, cudaS
     h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     CU(cudaEventRecord(h->ev[0], s));
     int r;
-    if (h->sweep) {  // no trace array: only the records other ranks need, straight into the send buffer
-        r = wxb_euler_edge_traces(a, h->n, s);
+    if (fused) {  // no trace array: only the records other ranks need, straight into the send buffer
+        r = euler_eq ? wxb_euler_edge_traces(a, h->n, s) : wxb_sw_tile_edge_traces(a, h->n, s);
     } else {
         r = h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_traces(a, h->n, s) : wxb_sw_traces(a, h->n, s);
         if (r == 0) r = wxb_pack(a, h->ntr, h->F, h->nfaces, h->cfg.equations == WXB_EQ_EULER3D, s);
@@ -411,10 +421,11 @@ int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs
     }
     EvalArgs a;
     fill_args(h, a, q, v, rhs0, dt, eps, mode, out);
+    const bool fused = use_fused(h, mode >= 0);
     if (part == 1 || part == 2) {
         if (h->cfg.nghost == 0) {
             if (part == 2) return WXB_OK;  // everything is inner
-        } else if (h->sweep) {
+        } else if (fused) {
             a.tlist = part == 1 ? h->d_tiles_inner : h->d_tiles_outer;
             a.ntiles = part == 1 ? h->nt_inner : h->nt_outer;
         } else {
@@ -425,7 +436,7 @@ int do_finish(wxb_handle* h, const double* q, const double* v, const double* rhs
         set_err(h, "part must be 0, 1 or 2");
         return WXB_EINVAL;
     }
-    int r = h->sweep ? wxb_euler_sweep(a, h->n, s)
+    int r = fused ? (h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_sweep(a, h->n, s) : wxb_sw_tile(a, h->n, s))
                      : (h->cfg.equations == WXB_EQ_EULER3D ? wxb_euler_main(a, h->n, s) : wxb_sw_main(a, h->n, s));
     if (r != 0) {
         set_err(h, "main kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -863,7 +874,8 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     const bool jvp = mode >= 0;
     int r = check_mode(h, d_q, jvp ? d_v : nullptr, jvp ? d_r0 : nullptr, eps, mode, d_out);
     if (r != WXB_OK) return r;
-    if (jvp && !h->d_qp && !h->sweep) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
+    const bool fused = use_fused(h, jvp);
+    if (jvp && !h->d_qp && !fused) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     const int nc = h->nchunk;
     // uploads, chunk by chunk
     for (int c = 0; c < nc; ++c) {
@@ -879,7 +891,7 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     cudaStream_t sc = h->s_cmp;
     CU(cudaEventRecord(h->ev[0], sc));
     auto traces = [&](int c) -> int {
-        if (h->sweep) return 0;  // the sweep kernel extrapolates from the state itself
+        if (fused) return 0;  // the fused kernel extrapolates from the state itself
         if (nc > 1) {
             at.elist = h->d_clist + h->chunk_off[c];
             at.nelist = h->chunk_off[c + 1] - h->chunk_off[c];
@@ -887,7 +899,8 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
         return euler ? wxb_euler_traces(at, h->n, sc) : wxb_sw_traces(at, h->n, sc);
     };
     auto maink = [&](int c) -> int {
-        if (h->sweep) {  // levels of chunk c; the levels either side of it have been uploaded (see the loop below)
+        if (fused && !euler) return wxb_sw_tile(am, h->n, sc);
+        if (fused) {  // levels of chunk c; the levels either side of it have been uploaded (see the loop below)
             am.k0 = h->chunk_k[c];
             am.k1 = h->chunk_k[c + 1];
             return wxb_euler_sweep(am, h->n, sc);

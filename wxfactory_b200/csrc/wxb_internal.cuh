@@ -84,7 +84,8 @@ struct wxb_handle {
     int *d_send, *d_elist_inner, *d_elist_outer;
     int n_inner, n_outer;
     // column-sweep path of the Euler equations (euler_sweep.cu): one launch per evaluation, no local trace array
-    bool sweep;
+    bool sweep;              // the fused path exists on this handle (euler_sweep.cu / sw_tile.cu)
+    bool split;              // the two-kernel path exists (euler3d.cu / sw2d.cu: trace array, element lists)
     double* d_fasttab;
     double* d_trace_alloc;   // what was really allocated for d_trace (sweep: the ghost records only)
     int *d_tiles_inner, *d_tiles_outer;
@@ -129,6 +130,9 @@ int wxb_sweep_configure(int n);
 void wxb_sweep_tile_shape(int n, int* tj, int* ti);
 int wxb_euler_sweep(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_edge_traces(const EvalArgs& a, int n, cudaStream_t s);
+void wxb_sw_tile_shape(int n, int* tj, int* ti);
+int wxb_sw_tile(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_sw_tile_edge_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_traces(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_main(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_pack(const EvalArgs& a, int ntr, int F, int nfaces, int elem_major, cudaStream_t s);

@@ -57,7 +57,11 @@ class RhsB200:
         self.num_var = problem.num_var
         # Euler: the fused column-sweep kernel (csrc/euler_sweep.cu, default) or the traces + main pair of
         # csrc/euler3d.cu (WXB_EULER_PATH=split); read by wxb_create
-        self.sweep = euler and os.environ.get("WXB_EULER_PATH", "sweep") != "split"
+        # one kernel path per handle (csrc/wxb_api.cu: build): fused (Euler "sweep", shallow water "tile") or "split"
+        fused = os.environ.get("WXB_EULER_PATH" if euler else "WXB_SW_PATH", "") != "split"
+        self._fused = (fused, fused)  # (RHS, JVP)
+        self.sweep = fused
+        self.path_name = ("sweep" if euler else "tile") if fused else "split"
         # trace fields per face point: the Euler kernels carry 6 (csrc/euler3d.cu, WXB_TRACE_FIELDS)
         self.num_trace = 6 if euler else 3
         nz = problem.nz if euler else 1
@@ -141,13 +145,14 @@ class RhsB200:
     def _check(self, code, what):
         capi.check(self._lib, self._h, code, what)
 
-    def _kernels_per_eval(self):
+    def _kernels_per_eval(self, jvp=False):
         adv = self.prob.equations == "euler" and self.prob.advection_only
         if adv:
             return 0
-        if self.sweep:  # one sweep launch (two on a multi-rank handle: inner, outer tiles) + the edge-trace kernel
-            return 1 + (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
-        return 2 + (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
+        multi = (1 if self.part.nsend else 0) + (1 if self.part.nghost else 0)
+        if self._fused[1 if jvp else 0]:  # one fused launch (two on a multi-rank handle: inner, outer tiles) + the edge traces
+            return 1 + multi
+        return 2 + multi  # traces (+ pack) and main (inner, outer)
 
     def _tm(self):
         if self._torch is None:
@@ -274,7 +279,7 @@ class RhsB200:
             self._check(self._lib.wxb_finish(self._h, q.data_ptr(), vp, rp, dt, eps, mode, 1, out.data_ptr(), sp), "wxb_finish")
             stream.wait_stream(cs)
             self._check(self._lib.wxb_finish(self._h, q.data_ptr(), vp, rp, dt, eps, mode, 2, out.data_ptr(), sp), "wxb_finish")
-        self.launches += self._kernels_per_eval()
+        self.launches += self._kernels_per_eval(mode >= 0)
         self._have_timing = True
         return out
 
@@ -321,7 +326,7 @@ class RhsB200:
                 self._lib.wxb_jvp_host(self._h, q.ctypes.data, v.ctypes.data, r.ctypes.data, float(dt), float(eps), m, out.ctypes.data),
                 "wxb_jvp_host",
             )
-            self.launches += self._kernels_per_eval()
+            self.launches += self._kernels_per_eval(True)
             return out.reshape(-1)
         q, _ = self._as_device(Q, "Q")
         v, _ = self._as_device(vec, "vec")
@@ -369,7 +374,7 @@ class RhsB200:
         out = self._host_result()
         m = capi.JVP_FD if mode == "fd" else capi.JVP_RAT
         self._check(self._lib.wxb_jvp_bound_host(self._h, v.ctypes.data, float(dt), float(eps), m, out.ctypes.data), "wxb_jvp_bound_host")
-        self.launches += self._kernels_per_eval()
+        self.launches += self._kernels_per_eval(True)
         return out
 
     # ---- timing vocabulary of the reference (rhs.py:68-73,190-213) ---------------------------------
