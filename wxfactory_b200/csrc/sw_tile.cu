@@ -30,7 +30,7 @@
 #define WXB_SWT_TI 8
 #endif
 #ifndef WXB_SWT_MINB
-#define WXB_SWT_MINB 4
+#define WXB_SWT_MINB 3
 #endif
 
 namespace {
@@ -119,17 +119,9 @@ __global__ void __launch_bounds__(TCfg<N>::THREADS, WXB_SWT_MINB) sw_tile(const 
     for (int t = tid; t < C::NOPS; t += NT) sm.op[t] = a.ops[t];
     const int tile = a.tlist ? a.tlist[blockIdx.x] : (int)blockIdx.x;
     const int nx = a.nx;
-    const int nti = (nx + TI - 1) / TI;
-    int s = 0, trem = tile;
-    for (int u = 0; u + 1 < a.st.nslabs; ++u) {
-        const int nt = ((a.st.ny[u] + TJ - 1) / TJ) * nti;
-        if (s == u && trem >= nt) {
-            trem -= nt;
-            s = u + 1;
-        }
-    }
+    const int4 ti4 = a.tinfo[tile];  // slab, first row, first column (built on the host at create)
+    const int s = ti4.x, tj0 = ti4.y, ti0 = ti4.z;
     const int ny = a.st.ny[s];
-    const int tj0 = (trem / nti) * TJ, ti0 = (trem % nti) * TI;
     const int aj = min(TJ, ny - tj0), ai = min(TI, nx - ti0);
     const long long vstride = (long long)ny * nx * P;
     const int sa = le / TI, sb = le - sa * TI;
@@ -293,7 +285,9 @@ __global__ void __launch_bounds__(TCfg<N>::THREADS, WXB_SWT_MINB) sw_tile(const 
         }
     }
 
-    // ---- stage ----
+    // ---- stage, and everything of the node that needs no neighbour: flux fields -> shared memory, forcing -> 2 registers
+    // (the 20 values loaded above die here, long before the edge phase) ----
+    double fo1 = 0.0, fo2 = 0.0, inv_sg = 1.0;
     if (active) {
         if (JVP) {
 #pragma unroll
@@ -304,6 +298,18 @@ __global__ void __launch_bounds__(TCfg<N>::THREADS, WXB_SWT_MINB) sw_tile(const 
         sm.so[0][tid] = h0;
         sm.so[1][tid] = q[1];
         sm.so[2][tid] = q[2];
+        const double ih = 1.0 / q[0];  // one reciprocal serves both velocities
+        const double u1 = q[1] * ih, u2 = q[2] * ih;
+        const double hsq = q[0] * q[0], hg = 0.5 * WXB_GRAVITY;
+        sm.fl[0][tid] = sg * q[1];
+        sm.fl[1][tid] = sg * (q[1] * u1 + hg * H11 * hsq);
+        sm.fl[2][tid] = sg * (q[2] * u1 + hg * H12 * hsq);
+        sm.fl[3][tid] = sg * q[2];
+        sm.fl[4][tid] = sg * (q[1] * u2 + hg * H12 * hsq);
+        sm.fl[5][tid] = sg * (q[2] * u2 + hg * H22 * hsq);
+        fo1 = 2.0 * (c[0] * q[1] + c[1] * q[2]) + c[2] * q[1] * u1 + 2.0 * c[3] * q[1] * u2 + WXB_GRAVITY * q[0] * (H11 * dz1 + H12 * dz2);
+        fo2 = 2.0 * (c[4] * q[1] + c[5] * q[2]) + 2.0 * c[6] * q[1] * u2 + c[7] * q[2] * u2 + WXB_GRAVITY * q[0] * (H12 * dz1 + H22 * dz2);
+        inv_sg = 1.0 / sg;
     }
 #pragma unroll
     for (int r = 0; r < HR; ++r) {
@@ -377,25 +383,11 @@ __global__ void __launch_bounds__(TCfg<N>::THREADS, WXB_SWT_MINB) sw_tile(const 
         for (int v = 0; v < NVAR; ++v) sm.ff[f][v][pt] = cf[v];
     }
 
-    // ---- nodes ----
-    const int ii = node % N, jj = node / N;
-    double u1 = 0, u2 = 0;
-    if (active) {
-        const double ih = 1.0 / q[0];  // one reciprocal serves both velocities
-        u1 = q[1] * ih;
-        u2 = q[2] * ih;
-        const double hsq = q[0] * q[0], hg = 0.5 * WXB_GRAVITY;
-        sm.fl[0][tid] = sg * q[1];
-        sm.fl[1][tid] = sg * (q[1] * u1 + hg * H11 * hsq);
-        sm.fl[2][tid] = sg * (q[2] * u1 + hg * H12 * hsq);
-        sm.fl[3][tid] = sg * q[2];
-        sm.fl[4][tid] = sg * (q[1] * u2 + hg * H12 * hsq);
-        sm.fl[5][tid] = sg * (q[2] * u2 + hg * H22 * hsq);
-    }
     __syncthreads();
     if (!active) return;
 
     // ---- finish ----
+    const int ii = node % N, jj = node / N;
     double acc[NVAR] = {0, 0, 0};
 #pragma unroll
     for (int d = 0; d < 2; ++d) {
@@ -413,11 +405,6 @@ __global__ void __launch_bounds__(TCfg<N>::THREADS, WXB_SWT_MINB) sw_tile(const 
 #pragma unroll
         for (int v = 0; v < NVAR; ++v) acc[v] += cw * sm.ff[flo][v][pt] + ce * sm.ff[fhi][v][pt];
     }
-    const double fo1 = 2.0 * (c[0] * q[1] + c[1] * q[2]) + c[2] * q[1] * u1 + 2.0 * c[3] * q[1] * u2 +
-                       WXB_GRAVITY * q[0] * (H11 * dz1 + H12 * dz2);
-    const double fo2 = 2.0 * (c[4] * q[1] + c[5] * q[2]) + 2.0 * c[6] * q[1] * u2 + c[7] * q[2] * u2 +
-                       WXB_GRAVITY * q[0] * (H12 * dz1 + H22 * dz2);
-    const double inv_sg = 1.0 / sg;
     double r[NVAR];
     r[0] = -inv_sg * acc[0];
     r[1] = -inv_sg * acc[1] - fo1;

@@ -252,7 +252,7 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
         int tj = 1, ti = 1;
         if (euler) wxb_sweep_tile_shape(n, &tj, &ti);
         else wxb_sw_tile_shape(n, &tj, &ti);
-        std::vector<int> tin, tout;
+        std::vector<int> tin, tout, tinfo;
         const int32_t ghost_base = (int32_t)(h->trace_local / h->F);
         int tile = 0;
         for (int s = 0; s < cfg->nslabs; ++s) {
@@ -266,9 +266,16 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
                             for (int f = 0; f < 4; ++f) g = g || (A->nbr[((size_t)f * h->C + c) * 4] >= ghost_base);
                         }
                     (g ? tout : tin).push_back(tile);
+                    for (int x : {s, j0, i0, 0}) tinfo.push_back(x);
                 }
         }
         h->nt_all = tile;
+        {
+            int* tmp = nullptr;
+            int r = upload(h, &tmp, tinfo.data(), tinfo.size());
+            if (r != WXB_OK) return r;
+            h->d_tinfo = (int4*)tmp;
+        }
         h->nt_inner = (int)tin.size();
         h->nt_outer = (int)tout.size();
         if (cfg->nghost > 0) {
@@ -352,6 +359,7 @@ void fill_args(wxb_handle* h, EvalArgs& a, const double* q, const double* v, con
     a.has_topo = h->cfg.has_topo;
     a.tau0 = h->cfg.damp_tau0;
     a.fasttab = h->d_fasttab;
+    a.tinfo = h->d_tinfo;
     a.tlist = nullptr;
     a.ntiles = h->nt_all;
     a.k0 = 0;
@@ -515,7 +523,7 @@ int wxb_destroy(wxb_handle* h) {
     if (h->d_metric) h->d_sqrtg = h->d_h = h->d_chris = h->d_idz = nullptr;  // views into d_metric
     void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
-                    h->d_elist_inner,      h->d_elist_outer, h->d_trace_alloc, h->d_sendbuf, h->d_fasttab, h->d_tiles_inner, h->d_tiles_outer, h->d_qp,  h->d_q,           h->d_v,
+                    h->d_elist_inner,      h->d_elist_outer, h->d_trace_alloc, h->d_sendbuf, h->d_fasttab, h->d_tiles_inner, h->d_tiles_outer, h->d_tinfo, h->d_qp,  h->d_q,           h->d_v,
                     h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist, h->d_expf};
     for (void* p : ptrs)
         if (p) cudaFree(p);

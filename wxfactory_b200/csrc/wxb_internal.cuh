@@ -59,6 +59,7 @@ struct EvalArgs {
     int nelist;
     // column-sweep path (euler_sweep.cu)
     const double* fasttab;  // log / exp tables (fastmath.cuh)
+    const int4* tinfo;      // per tile: slab, first row, first column of the tile (built at create)
     const int* tlist;       // optional list of tiles to process (nullptr = all)
     int ntiles;             // blocks to launch
     int k0, k1;             // levels [k0, k1) to sweep
@@ -89,6 +90,7 @@ struct wxb_handle {
     double* d_fasttab;
     double* d_trace_alloc;   // what was really allocated for d_trace (sweep: the ghost records only)
     int *d_tiles_inner, *d_tiles_outer;
+    int4* d_tinfo;
     int nt_all, nt_inner, nt_outer;
     double *d_trace, *d_sendbuf, *d_qp;
     int64_t trace_local;  // doubles in the local part of the trace array
