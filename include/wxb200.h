@@ -125,6 +125,11 @@ int wxb_create(const wxb_config* cfg, const wxb_static_arrays* arrays, int devic
 int wxb_destroy(wxb_handle* h);
 const char* wxb_last_error(const wxb_handle* h); /* h may be NULL: last create error */
 
+/* 1 if the handle runs the fused kernel (Euler: euler_sweep.cu, shallow water: sw_tile.cu), 0 if the traces + main pair.
+ * Chosen at create: env WXB_EULER_PATH / WXB_SW_PATH = sweep | tile | split, else the path that measured faster for the
+ * order (no reference counterpart: the reference has one numpy path). */
+int wxb_handle_fused(const wxb_handle* h);
+
 /* sizes, in doubles */
 int64_t wxb_state_size(const wxb_handle* h);      /* num_var * E * P                                  */
 int64_t wxb_send_size(const wxb_handle* h);       /* nsend  * ntr * nz * F  (ntr trace fields: Euler 6, SW 3) */

@@ -214,12 +214,12 @@ def test_timings_vocabulary(rhs_cache):
     assert len(rhs.timings) >= 1 and all(t[2] > 0 for t in rhs.timings)
 
 
-@pytest.mark.parametrize("env", [{"WXB_EULER_PATH": "split", "WXB_SW_PATH": "split"}])
+@pytest.mark.parametrize("env", [{"WXB_EULER_PATH": "split", "WXB_SW_PATH": "split"}, {"WXB_EULER_PATH": "sweep", "WXB_SW_PATH": "tile"}])
 def test_other_kernel_paths_match_too(env):
-    """By default an Euler handle runs the fused column-sweep kernel (csrc/euler_sweep.cu) and a shallow-water handle the
-    fused tile kernel (csrc/sw_tile.cu).  WXB_EULER_PATH = split / WXB_SW_PATH = split select the traces + main pairs
-    (csrc/euler3d.cu, csrc/sw2d.cu) per process: run the device-path, JVP and host-pipeline parity cases again in a
-    child process with them."""
+    """A handle runs ONE kernel path, chosen at create: the fused kernel (Euler: csrc/euler_sweep.cu, default at the orders
+    where it measured faster, n = 2 and 4; shallow water: csrc/sw_tile.cu) or the traces + main pair (csrc/euler3d.cu,
+    csrc/sw2d.cu).  WXB_EULER_PATH / WXB_SW_PATH force one for every order, per process: run the device-path, JVP and
+    host-pipeline parity cases again in a child process with each, so that both paths are checked at every order."""
     import subprocess
     import sys
 

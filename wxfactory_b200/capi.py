@@ -71,6 +71,7 @@ EXPORTS = [
     "wxb_create",
     "wxb_destroy",
     "wxb_last_error",
+    "wxb_handle_fused",
     "wxb_state_size",
     "wxb_send_size",
     "wxb_recv_size",
@@ -121,6 +122,7 @@ def load():
     lib.wxb_version.restype = i32
     lib.wxb_create.argtypes = [ctypes.POINTER(WxbConfig), ctypes.POINTER(WxbStaticArrays), i32, ctypes.POINTER(vp)]
     lib.wxb_destroy.argtypes = [vp]
+    lib.wxb_handle_fused.argtypes = [vp]
     lib.wxb_last_error.argtypes = [vp]
     lib.wxb_last_error.restype = ctypes.c_char_p
     for f in ("wxb_state_size", "wxb_send_size", "wxb_recv_size"):

@@ -13,6 +13,11 @@
 
 namespace {
 
+// orders whose Euler handles run the fused column-sweep kernel by default (the others run the traces + main pair)
+#ifndef WXB_SWEEP_DEFAULT
+#define WXB_SWEEP_DEFAULT(n) ((n) == 2 || (n) == 4)
+#endif
+
 char g_create_err[512] = "";
 void comm_free(wxb_handle* h);
 
@@ -227,7 +232,9 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     // a mixed mode (RHS fused, JVP pair) was measured faster and broke the Krylov iteration counts of Epi(2) on dcmip31.
     {
         const char* pe = getenv(euler ? "WXB_EULER_PATH" : "WXB_SW_PATH");
-        h->split = pe && strcmp(pe, "split") == 0;
+        // default per order: the path that measured faster (profiles/r02_sweep_orders.jsonl, r02_order_variants.log)
+        const bool fused_default = euler ? WXB_SWEEP_DEFAULT(n) : true;
+        h->split = pe ? strcmp(pe, "split") == 0 : !fused_default;
         h->sweep = !h->split;
     }
     // trace array: local part (SW [ntr][nfaces][E][F], Euler [E][nfaces][ntr][F]), then the ghost records
@@ -543,6 +550,8 @@ int wxb_destroy(wxb_handle* h) {
     delete h;
     return WXB_OK;
 }
+
+int wxb_handle_fused(const wxb_handle* h) { return h ? (h->sweep ? 1 : 0) : WXB_EINVAL; }
 
 int64_t wxb_state_size(const wxb_handle* h) { return h ? (int64_t)h->nvar * h->E * h->P : 0; }
 int64_t wxb_send_size(const wxb_handle* h) {

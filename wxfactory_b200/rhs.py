@@ -57,11 +57,7 @@ class RhsB200:
         self.num_var = problem.num_var
         # Euler: the fused column-sweep kernel (csrc/euler_sweep.cu, default) or the traces + main pair of
         # csrc/euler3d.cu (WXB_EULER_PATH=split); read by wxb_create
-        # one kernel path per handle (csrc/wxb_api.cu: build): fused (Euler "sweep", shallow water "tile") or "split"
-        fused = os.environ.get("WXB_EULER_PATH" if euler else "WXB_SW_PATH", "") != "split"
-        self._fused = (fused, fused)  # (RHS, JVP)
-        self.sweep = fused
-        self.path_name = ("sweep" if euler else "tile") if fused else "split"
+        self._euler = euler
         # trace fields per face point: the Euler kernels carry 6 (csrc/euler3d.cu, WXB_TRACE_FIELDS)
         self.num_trace = 6 if euler else 3
         nz = problem.nz if euler else 1
@@ -103,6 +99,12 @@ class RhsB200:
         capi.check(self._lib, None, code, "wxb_create")
         self._h = h
         self._static = None
+        # one kernel path per handle, chosen at create (csrc/wxb_api.cu: build): fused (Euler "sweep", shallow water "tile")
+        # or the traces + main pair ("split")
+        fused = bool(self._lib.wxb_handle_fused(self._h))
+        self._fused = (fused, fused)  # (RHS, JVP)
+        self.sweep = fused
+        self.path_name = ("sweep" if euler else "tile") if fused else "split"
         self.size = int(self._lib.wxb_state_size(self._h))
         self.timestamps = []
         self.timings = []
