@@ -62,3 +62,20 @@ def test_implicit_and_exponential_steps_follow_reference(name, case, kind):
     # the initial state by 2e-16 relative moves this result by 1.4e-8 (same code, same machine), so the bound there is the
     # solver tolerance 1e-7 (measured 3.3e-8 after 10 steps)
     assert _rel(Q.numpy(), g["QN"]) <= (1e-10 if kind == "ros2" else 1e-7 if name == "epi3_case6" else 1e-8)
+
+
+def test_epi_refuses_the_complex_step_jacobian(golden):
+    """the reference's schema default is jacobian_method = complex; Epi must not silently run the FD product
+    for a Configuration handed over unchanged.  And Integrator.step resets solver_info like integrator.py:107-108."""
+    import types
+
+    import pytest
+
+    from wxfactory_b200 import integrators
+
+    param = types.SimpleNamespace(tolerance=1e-7, exponential_solver="kiops", jacobian_method="complex", verbose_solver=0)
+    with pytest.raises(TypeError):
+        integrators.Epi(param, 2, lambda q: q, ops=CpuVecOps())
+    param.jacobian_method = "fd"
+    integ = integrators.Epi(param, 2, lambda q: q, ops=CpuVecOps())
+    assert integ.solver_info is None and integ.last_solver_info is None

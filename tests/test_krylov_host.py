@@ -104,3 +104,15 @@ def test_pmex_reaches_mmax_rows():
     A[:n, n] = u[1]
     want = scipy.linalg.expm(A)[:n] @ numpy.concatenate([u[0], [1.0]])
     assert numpy.linalg.norm(w.numpy()[0] - want) <= 1e-5 * numpy.linalg.norm(want)
+
+
+def test_pmex_rejects_an_unusable_error_estimate():
+    """the reference's pmex takes math.log / math.ceil of its error estimate and raises when that is NaN or
+    infinite (pmex.py:283-300); the port raises a ValueError instead of carrying the NaN into the Krylov size."""
+    import pytest
+
+    n = 50
+    bad = lambda v: _t(numpy.full(n, numpy.nan))  # noqa: E731
+    u = numpy.vstack([numpy.ones(n), numpy.ones(n)])
+    with numpy.errstate(all="ignore"), pytest.raises(ValueError):
+        pmex([1.0], bad, _t(u), tol=1e-7, m_init=4, mmin=4, mmax=8, ops=CpuVecOps())

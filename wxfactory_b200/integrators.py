@@ -42,6 +42,7 @@ class Integrator:
         self.filter = filter  # optional ExpFilterB200 applied after every step (simulation.py:148)
         self.verbose_solver = getattr(param, "verbose_solver", 0)
         self.solver_info = None
+        self.last_solver_info = None
         self.sim_time = -1.0
         self.failure_flag = 0
         self.num_completed_steps = 0
@@ -64,6 +65,9 @@ class Integrator:
         self.latest_time = time() - t0
         self.sim_time += dt
         self.num_completed_steps += 1
+        # integrator.py:107-108 resets solver_info after handing it to the output manager; here there is no output manager:
+        # the step's report stays readable as last_solver_info and solver_info is reset like the reference's
+        self.last_solver_info, self.solver_info = self.solver_info, None
         return result
 
     def check_finite(self, Q):
@@ -172,6 +176,12 @@ class Epi(Integrator):
     def __init__(self, param, order, rhs, init_method=None, init_substeps=1, **kwargs):
         super().__init__(param, rhs, **kwargs)
         self.rhs = rhs
+        # the reference's schema default is the complex-step product (epi.py:103-104 passes param.jacobian_method on); this
+        # path provides the finite-difference one only: a Configuration handed over unchanged must not silently get another
+        # Jacobian approximation
+        method = getattr(param, "jacobian_method", "fd")
+        if method != "fd":
+            raise TypeError(f"jacobian_method = {method!r}: the B200 path implements the finite-difference JVP only (set jacobian_method = fd)")
         self.tol = param.tolerance
         self.krylov_size = 1
         self.exponential_solver = getattr(param, "exponential_solver", "kiops")

@@ -428,6 +428,10 @@ def pmex(tau_out, A, u, tol=1e-7, delta=1.2, m_init=10, mmin=10, mmax=128, reuse
             err = abs(beta * nrm * F[j - 1, j])
             old_ohm = ohm
             ohm = numpy.float64(tau_end * err / (tau * tol))
+            if not numpy.isfinite(ohm) or ohm <= 0.0:
+                # pmex.py:283-300 uses math.log / math.ceil here, which raise on a vanishing, infinite or NaN error estimate;
+                # numpy would carry the NaN into the Krylov size instead
+                raise ValueError(f"pmex: error estimate {float(err)!r} gives no usable step-size control (omega = {float(ohm)!r})")
             order = float(numpy.log(numpy.float64(err) / err_half) / math.log(2))
             if m != old_m and tau == old_tau and ireject >= 1:
                 kest = max(1.1, (ohm / old_ohm) ** (1 / (old_m - m)))

@@ -48,7 +48,7 @@ class _DevPtr:
 class RhsB200:
     """dQ/dt = RHS(Q) on the cubed sphere for one rank of a 1/2/4/8-way partition."""
 
-    def __init__(self, problem, nranks=1, rank=0, device=0, process_group=None):
+    def __init__(self, problem, nranks=1, rank=0, device=0, process_group=None, defer_comm=False):
         self.prob = problem
         self.nranks, self.rank = int(nranks), int(rank)
         self.device_index = int(device)
@@ -116,7 +116,13 @@ class RhsB200:
         # multi-rank handles: the halo exchange runs inside the library (wxb_comm_init / wxb_eval_dist: NCCL send / recv on
         # the handle's own stream).  WXB_HALO=torch keeps the torch.distributed point-to-point exchange of halo.py.
         self._lib_comm = False
-        if self.nranks > 1 and os.environ.get("WXB_HALO", "lib") != "torch":
+        if not defer_comm:
+            self.init_comm()
+
+    def init_comm(self):
+        """Collective over the ranks of the handle's group (the constructor calls it unless ``defer_comm``: a caller that
+        staggers the construction of its ranks -- the set-up holds the static arrays on the host -- joins afterwards)."""
+        if self.nranks > 1 and not self._lib_comm and os.environ.get("WXB_HALO", "lib") != "torch":
             self._init_lib_comm()
 
     # ---- lifetime ---------------------------------------------------------------------------------
