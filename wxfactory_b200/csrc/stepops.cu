@@ -36,81 +36,141 @@ constexpr int MD_ROWS = 8;           // basis rows per pass of the multi-dot ker
                                      // values: 8 rows 2.3 ms for 22 x 2 products, 12 rows 4.9 ms (12 widely spaced streams per thread)
 
 // ------------------------------------------------------------------------------------------------------
-// exponential filter: one thread per node and variable pass; element fields staged in shared memory
+// exponential filter.  One thread owns one LINE of N nodes of an element in each of the three passes, so that every
+// pass reads and writes each value once (a thread per node reads each value N times from shared memory, which is what
+// bound the round-1 kernel: 120 B of shared-memory traffic per node and variable against 32 B here).
+//   pass x: thread (j,k) loads its line of q and sqrtG straight from global memory (N contiguous doubles), filters it
+//           in registers, stores it to shared memory;
+//   pass y: thread (i,k) filters its line in shared memory, in place;
+//   pass z: thread (i,j) reads its line, filters it, scales by 1/sqrtG and writes the result to global memory.
+// Plane stride N*N + N: the 16 lines (i,k) of an element then fall in 16 different 8-byte banks in pass y (n = 4).
 template <int N>
-__global__ void __launch_bounds__(N* N* N <= 64 ? 256 : N * N * N) expfilter_kernel(const EvalArgs a, const double* __restrict__ filt,
-                                                                                   const double* __restrict__ metric) {
-    constexpr int P = N * N * N, NV = 5;
-    constexpr int EB = P <= 64 ? 256 / P : 1;  // elements per block
-    __shared__ double s_f[N * N];
-    __shared__ double s_a[EB][NV][P];
-    __shared__ double s_b[EB][NV][P];
-    const int le = threadIdx.x / P, node = threadIdx.x % P;
-    const int e = blockIdx.x * EB + le;
-    const bool active = le < EB && e < a.E;
-    for (int t = threadIdx.x; t < N * N; t += blockDim.x) s_f[t] = filt[t];
-    double sg = 1.0;
+struct FiltCfg {
+    static constexpr int P = N * N * N, NV = 5, L = N * N;           // L lines per element and pass
+    static constexpr int EB = (256 / L) < 1 ? 1 : 256 / L;           // elements per block
+    static constexpr int THREADS = EB * L;
+    static constexpr int S = N * N + N;                              // padded k-plane stride
+    static constexpr int ELEM = N * S;                               // doubles per element and variable
+    static constexpr size_t SMEM = (size_t)EB * NV * ELEM * sizeof(double);
+};
+
+// the lines of an element exchange values only among themselves: when a warp holds whole elements (N = 2, 4) a warp
+// barrier is enough and the warps of a block run the three passes independently of one another
+template <int L>
+__device__ __forceinline__ void filt_sync() {
+    if constexpr (32 % L == 0) __syncwarp();
+    else __syncthreads();
+}
+
+template <int N, bool VEC>  // VEC: N even and 16-byte aligned arrays, the pass-x loads are 128-bit
+__global__ void __launch_bounds__(FiltCfg<N>::THREADS) expfilter_kernel(const EvalArgs a, const double* __restrict__ filt,
+                                                                        const double* __restrict__ metric) {
+    using C = FiltCfg<N>;
+    constexpr int P = C::P, NV = C::NV, L = C::L, S = C::S;
+    extern __shared__ __align__(16) double s_x[];  // [EB][NV][N planes][S]
+    const int le = threadIdx.x / L, line = threadIdx.x % L;
+    const int e = blockIdx.x * C::EB + le;
+    const bool active = e < a.E;
+    const int la = line % N, lb = line / N;  // the two fixed coordinates of this thread's lines
+    double f[N][N];                          // the filter matrix, kept in registers by every thread
+#pragma unroll
+    for (int r = 0; r < N; ++r)
+#pragma unroll
+        for (int m = 0; m < N; ++m) f[r][m] = filt[r * N + m];
+    double* se = s_x + (size_t)le * NV * C::ELEM;
     long long qo = 0, vst = 0;
+    const double* mrow = nullptr;
     if (active) {
         const ElemPos ep = decode_elem(a.st, e, a.nz, a.nx, P, NV);
-        qo = ep.qoff + node;
+        qo = ep.qoff;
         vst = ep.vstride;
-        sg = metric[(long long)e * (35 * P) + 27 * P + node];  // row sqrtG of the element-major metric block
-        double x[NV];
+        mrow = metric + (long long)e * (35 * P) + 27 * P;  // row sqrtG of the element-major metric block
+        // pass x: line (j = la, k = lb), nodes lb N^2 + la N + 0..N-1
+        const int n0 = lb * N * N + la * N;
+        double sg[N], x[NV][N];
+        if constexpr (VEC) {
 #pragma unroll
-        for (int v = 0; v < NV; ++v) x[v] = a.q[qo + v * vst];
+            for (int i = 0; i < N; i += 2) {
+                const double2 t = __ldg(reinterpret_cast<const double2*>(mrow + n0 + i));
+                sg[i] = t.x, sg[i + 1] = t.y;
+            }
 #pragma unroll
-        for (int v = 0; v < NV; ++v) s_a[le][v][node] = sg * x[v];
-    }
-    __syncthreads();
-    const int ii = node % N, jj = (node / N) % N, kk = node / (N * N);
-    double fi[N], fj[N], fk[N];  // this node's three filter rows, read once (the passes are shared-memory bound)
+            for (int v = 0; v < NV; ++v)
 #pragma unroll
-    for (int m = 0; m < N; ++m) {
-        fi[m] = s_f[ii * N + m];
-        fj[m] = s_f[jj * N + m];
-        fk[m] = s_f[kk * N + m];
-    }
-    // expfilter_new = (filter_x @ filter_y) @ filter_z with filter_d = kron(.., expfilter, ..).T: the passes commute
-    // in exact arithmetic; x, y, z is the order of the reference's product (operators.py:115-119)
-    if (active) {
+                for (int i = 0; i < N; i += 2) {
+                    const double2 t = *reinterpret_cast<const double2*>(a.q + qo + v * vst + n0 + i);
+                    x[v][i] = t.x, x[v][i + 1] = t.y;
+                }
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; ++i) sg[i] = mrow[n0 + i];
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+#pragma unroll
+                for (int i = 0; i < N; ++i) x[v][i] = a.q[qo + v * vst + n0 + i];
+        }
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
-            double s = 0.0;
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(fi[m], s_a[le][v][node - ii + m], s);
-            s_b[le][v][node] = s;
+            for (int i = 0; i < N; ++i) x[v][i] *= sg[i];
+#pragma unroll
+            for (int r = 0; r < N; ++r) {
+                double t = 0.0;
+#pragma unroll
+                for (int m = 0; m < N; ++m) t = fma(f[r][m], x[v][m], t);
+                se[v * C::ELEM + lb * S + la * N + r] = t;
+            }
         }
     }
-    __syncthreads();
+    filt_sync<L>();
     if (active) {
+        // pass y: line (i = la, k = lb), in place
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
-            double s = 0.0;
+            double* ln = se + v * C::ELEM + lb * S + la;
+            double x[N];
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(fj[m], s_b[le][v][node + (m - jj) * N], s);
-            s_a[le][v][node] = s;
+            for (int m = 0; m < N; ++m) x[m] = ln[m * N];
+#pragma unroll
+            for (int r = 0; r < N; ++r) {
+                double t = 0.0;
+#pragma unroll
+                for (int m = 0; m < N; ++m) t = fma(f[r][m], x[m], t);
+                ln[r * N] = t;
+            }
         }
     }
-    __syncthreads();
+    filt_sync<L>();
     if (active) {
-        const double inv = 1.0 / sg;  // metric.inv_sqrtG_new (metric3d.py:1157)
+        // pass z: line (i = la, j = lb); consecutive threads write consecutive nodes of each k plane
+        double inv[N];
+#pragma unroll
+        for (int k = 0; k < N; ++k) inv[k] = 1.0 / mrow[k * N * N + line];  // metric.inv_sqrtG_new (metric3d.py:1157)
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
-            double s = 0.0;
+            const double* ln = se + v * C::ELEM + line;
+            double x[N];
 #pragma unroll
-            for (int m = 0; m < N; ++m) s = fma(fk[m], s_a[le][v][node + (m - kk) * N * N], s);
-            a.out[qo + v * vst] = s * inv;
+            for (int m = 0; m < N; ++m) x[m] = ln[m * S];
+#pragma unroll
+            for (int r = 0; r < N; ++r) {
+                double t = 0.0;
+#pragma unroll
+                for (int m = 0; m < N; ++m) t = fma(f[r][m], x[m], t);
+                a.out[qo + v * vst + r * N * N + line] = t * inv[r];
+            }
         }
     }
 }
 
 template <int N>
 int launch_expfilter(const EvalArgs& a, const double* filt, const double* metric, cudaStream_t s) {
-    constexpr int P = N * N * N;
-    constexpr int EB = P <= 64 ? 256 / P : 1;
-    constexpr int threads = P <= 64 ? 256 : P;
-    expfilter_kernel<N><<<(a.E + EB - 1) / EB, threads, 0, s>>>(a, filt, metric);
+    using C = FiltCfg<N>;
+    const bool vec = N % 2 == 0 && (((uintptr_t)a.q | (uintptr_t)metric) & 15) == 0;
+    auto kern = vec ? expfilter_kernel<N, (N % 2 == 0)> : expfilter_kernel<N, false>;
+    if (C::SMEM > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM) != cudaSuccess)
+        return -1;
+    kern<<<(a.E + C::EB - 1) / C::EB, C::THREADS, C::SMEM, s>>>(a, filt, metric);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
