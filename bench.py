@@ -409,9 +409,16 @@ def run_b200(args):
     r0_h.copy_(rhs0_d)
     torch.cuda.synchronize()
 
+    host_call_s = [0.0, 0.0]  # wall time inside the two public calls of the end-to-end step (both return synchronised)
+
     def step_host():
+        t0 = time.perf_counter()
         op = rhs.linearize(q_h.numpy(), dt, mode="fd")  # RHS(Q) comes back; (Q, RHS(Q)) stay as the operator's point
-        return op.rhs, op(v_h.numpy())
+        t1 = time.perf_counter()
+        jv = op(v_h.numpy())
+        host_call_s[0] += t1 - t0
+        host_call_s[1] += time.perf_counter() - t1
+        return op.rhs, jv
 
     sampler = ClockSampler(range(world)) if rank == 0 else None
     if sampler:
@@ -449,6 +456,7 @@ def run_b200(args):
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
     for _ in range(2):
         step_host()
+    host_call_s[0] = host_call_s[1] = 0.0
     ms_e2e, e2e_win = timed_loop(step_host, e2e_steps)
     if sampler:
         time.sleep(0.2)
@@ -525,13 +533,15 @@ def run_b200(args):
                 "d2h_bytes_per_step": 2 * state_bytes,
                 "steps": e2e_steps,
                 "ms_per_step": ms_e2e / e2e_steps,
+                "host_call_ms": {"linearize": host_call_s[0] * 1e3 / e2e_steps, "apply": host_call_s[1] * 1e3 / e2e_steps,
+                                 "what": "rank 0's wall time inside the two calls of a step (a multi-rank call ends when the slowest neighbour has sent its records)"},
                 "how": (
                     "op = RhsB200.linearize(Q numpy, dt) [Q up, RHS(Q) down, both kept on the device as the operator's "
                     "linearisation point, as MatvecOp captures them]; op(v numpy) [v up, J v down] -> wxb_linearize_host / "
                     "wxb_jvp_bound_host, state moved in chunks of levels on 3 streams; pinned host arrays in, numpy out"
                     if world == 1
-                    else "op = RhsB200.linearize(Q numpy, dt) [Q up, RHS(Q) down, both kept on the device with the operator]; op(v numpy) "
-                    "[v up, J v down]; whole-state copies from / to pinned host arrays around wxb_eval_dist (halo exchange inside)"
+                    else "the same two calls on every rank (collective): level chunks up, the records other ranks need formed and exchanged "
+                    "chunk by chunk over NCCL inside the library, sweeps and downloads behind them (wxb_api.cu: pipelined_eval)"
                 ),
             },
             "gpu_launches": int(launches),

@@ -775,14 +775,17 @@ __global__ void __launch_bounds__(SCfg<N>::THREADS, SCfg<N>::MINB) euler_sweep(c
 
 // ------------------------------------------------------------------------------------------------------
 // Trace records for OTHER ranks (multi-rank handles): the same staged rows and the same form_trace as the sweep, for
-// the (column, face) pairs of the send list only.  One block per (record, level); sendbuf[rec][k][field][F].
+// the (column, face) pairs of the send list only.  One block per (record, level) for the levels [k0, k1) of the call;
+// sendbuf[rec][k - k0][field][F] (k0 = 0, k1 = nz: the layout the ghost records have on the receiving rank; the host
+// pipeline sends level chunks, each chunk's records behind one another, and unpacks on arrival: wxb_unpack_ghost).
 template <int N, bool JVP>
 __global__ void __launch_bounds__(N* N* N) euler_edge_traces(const EvalArgs a) {
     constexpr int P = N * N * N, F = N * N;
     __shared__ double srow[NSTAGE][P];
     __shared__ double s_ext[2 * N];
     __shared__ double s_tab[WXB_FASTTAB_DOUBLES];
-    const int rec = blockIdx.x / a.nz, k = blockIdx.x - rec * a.nz;
+    const int kc = a.k1 - a.k0;
+    const int rec = blockIdx.x / kc, kl = blockIdx.x - rec * kc, k = a.k0 + kl;
     const int node = threadIdx.x;
     for (int t = node; t < WXB_FASTTAB_DOUBLES; t += P) s_tab[t] = a.fasttab[t];
     if (node < 2 * N) s_ext[node] = a.ops[node];
@@ -816,10 +819,22 @@ __global__ void __launch_bounds__(N* N* N) euler_edge_traces(const EvalArgs a) {
     if (node < F) {
         double o6[NTR];
         form_trace<N>(&srow[0][0], P, s_ext + (f & 1) * N, f >> 1, node, s_tab + WXB_EXPTAB_OFF, o6);
-        double* dst = a.sendbuf + (((long long)rec * a.nz + k) * NTR) * F + node;
+        double* dst = a.sendbuf + (((long long)rec * kc + kl) * NTR) * F + node;
 #pragma unroll
         for (int v = 0; v < NTR; ++v) dst[v * F] = o6[v];
     }
+}
+
+// ghost[(g nz + k) rec + x] = stage[(g kc + k - k0) rec + x] for the levels of one chunk (rec = NTR F doubles)
+__global__ void __launch_bounds__(256) unpack_ghost(const double* __restrict__ stage, double* __restrict__ ghost, long long total, int rec,
+                                                   int kc, int k0, int nz) {
+    const long long t = blockIdx.x * 256LL + threadIdx.x;
+    if (t >= total) return;
+    const long long r = t / rec;
+    const int x = (int)(t - r * rec);
+    const long long g = r / kc;
+    const int kl = (int)(r - g * kc);
+    ghost[(g * nz + k0 + kl) * rec + x] = stage[t];
 }
 
 template <int N>
@@ -836,11 +851,11 @@ int launch_sweep(const EvalArgs& a, cudaStream_t s) {
 
 template <int N>
 int launch_edge(const EvalArgs& a, cudaStream_t s) {
-    if (a.nsend == 0) return 0;
+    if (a.nsend == 0 || a.k1 <= a.k0) return 0;
     if (a.v)
-        euler_edge_traces<N, true><<<a.nsend * a.nz, N * N * N, 0, s>>>(a);
+        euler_edge_traces<N, true><<<a.nsend * (a.k1 - a.k0), N * N * N, 0, s>>>(a);
     else
-        euler_edge_traces<N, false><<<a.nsend * a.nz, N * N * N, 0, s>>>(a);
+        euler_edge_traces<N, false><<<a.nsend * (a.k1 - a.k0), N * N * N, 0, s>>>(a);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
@@ -884,6 +899,13 @@ int wxb_euler_sweep(const EvalArgs& a, int n, cudaStream_t s) {
         case 6: return launch_sweep<6>(a, s);
     }
     return -1;
+}
+
+int wxb_unpack_ghost(const double* stage, double* ghost, int nghost, int rec, int k0, int k1, int nz, cudaStream_t s) {
+    const long long total = (long long)nghost * (k1 - k0) * rec;
+    if (total <= 0) return 0;
+    unpack_ghost<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(stage, ghost, total, rec, k1 - k0, k0, nz);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 int wxb_euler_edge_traces(const EvalArgs& a, int n, cudaStream_t s) {

@@ -531,7 +531,7 @@ int wxb_destroy(wxb_handle* h) {
     void* ptrs[] = {h->d_ops,  h->d_sqrtg, h->d_h,        h->d_chris, h->d_idz,         h->d_damp,        h->d_topo, h->d_metric,
                     h->d_fmi,  h->d_fmj,   h->d_fmk,      h->d_topo_itf, h->d_xform,    h->d_nbr,         h->d_send,
                     h->d_elist_inner,      h->d_elist_outer, h->d_trace_alloc, h->d_sendbuf, h->d_fasttab, h->d_tiles_inner, h->d_tiles_outer, h->d_tinfo, h->d_qp,  h->d_q,           h->d_v,
-                    h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist, h->d_expf};
+                    h->d_r0,   h->d_out, h->d_lq, h->d_lr, h->d_clist, h->d_expf, h->d_recv_stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int r = 0; r < WXB_TIMING_RING; ++r)
@@ -542,6 +542,8 @@ int wxb_destroy(wxb_handle* h) {
         for (int c = 0; c < h->nchunk; ++c) {
             cudaEventDestroy(h->ev_in[c]);
             cudaEventDestroy(h->ev_main[c]);
+            if (h->ev_packed_c[c]) cudaEventDestroy(h->ev_packed_c[c]);
+            if (h->ev_halo_c[c]) cudaEventDestroy(h->ev_halo_c[c]);
         }
         cudaStreamDestroy(h->s_in);
         cudaStreamDestroy(h->s_cmp);
@@ -862,6 +864,13 @@ static int pipe_setup(wxb_handle* h) {
         CU(cudaEventCreateWithFlags(&h->ev_in[c], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_main[c], cudaEventDisableTiming));
     }
+    if (h->cfg.nghost != 0 || h->cfg.nsend != 0) {
+        for (int c = 0; c < h->nchunk; ++c) {
+            CU(cudaEventCreateWithFlags(&h->ev_packed_c[c], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->ev_halo_c[c], cudaEventDisableTiming));
+        }
+        if (h->cfg.nghost > 0) CU(cudaMalloc((void**)&h->d_recv_stage, (size_t)h->cfg.nghost * h->ntr * nz * h->F * sizeof(double)));
+    }
     h->pipe_ready = true;
     return WXB_OK;
 }
@@ -883,7 +892,30 @@ static int chunk_copy(wxb_handle* h, int c, double* dst, const double* src, cuda
     return WXB_OK;
 }
 
+static bool has_remote(const wxb_handle* h) { return h->cfg.nghost != 0 || h->cfg.nsend != 0; }
+
+// Multi-rank handle on a path the level pipeline does not cover (pair of kernels, shallow water): whole arrays up,
+// wxb_eval_dist, whole array down -- still one library call, the exchange overlapped with the inner elements.
+static int whole_array_dist_eval(wxb_handle* h, double* d_q, const double* q_host, double* d_v, const double* v_host, double* d_r0,
+                                 const double* r0_host, double dt, double eps, int mode, double* d_out, double* out_host) {
+    CU(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)wxb_state_size(h) * sizeof(double);
+    cudaStream_t sc = h->s_cmp;
+    if (q_host) CU(cudaMemcpyAsync(d_q, q_host, bytes, cudaMemcpyHostToDevice, sc));
+    if (mode >= 0 && v_host) CU(cudaMemcpyAsync(d_v, v_host, bytes, cudaMemcpyHostToDevice, sc));
+    if (mode >= 0 && r0_host) CU(cudaMemcpyAsync(d_r0, r0_host, bytes, cudaMemcpyHostToDevice, sc));
+    int r = wxb_eval_dist(h, d_q, mode >= 0 ? d_v : nullptr, mode >= 0 ? d_r0 : nullptr, dt, eps, mode, d_out, sc);
+    if (r != WXB_OK) return r;
+    if (out_host) CU(cudaMemcpyAsync(out_host, d_out, bytes, cudaMemcpyDeviceToHost, sc));
+    CU(cudaStreamSynchronize(sc));
+    return WXB_OK;
+}
+
 // One evaluation with host operands.  *_host == nullptr means "already on the device" (in the matching d_* array).
+// Multi-rank handles on the fused Euler path: the halo exchange is cut into the same level chunks.  As soon as chunk
+// c has arrived, euler_edge_traces forms the records other ranks need of ITS levels (a record is level-local), NCCL
+// moves them on the handle's communication stream and wxb_unpack_ghost files them under the ghost records; the sweep of
+// chunk c-1 follows.  Uploads, exchange, sweeps and downloads of different chunks overlap as on one rank.
 static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, double* d_v, const double* v_host, double* d_r0,
                           const double* r0_host, double dt, double eps, int mode, double* d_out, double* out_host) {
     CU(cudaSetDevice(h->device));
@@ -892,6 +924,9 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     int r = check_mode(h, d_q, jvp ? d_v : nullptr, jvp ? d_r0 : nullptr, eps, mode, d_out);
     if (r != WXB_OK) return r;
     const bool fused = use_fused(h, jvp);
+    const bool dist = has_remote(h);
+    if (dist && !(fused && euler && h->nchunk > 1))
+        return whole_array_dist_eval(h, d_q, q_host, d_v, v_host, d_r0, r0_host, dt, eps, mode, d_out, out_host);
     if (jvp && !h->d_qp && !fused) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     const int nc = h->nchunk;
     // uploads, chunk by chunk
@@ -907,6 +942,35 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     h->ev = h->ev_ring[h->nevals % WXB_TIMING_RING];
     cudaStream_t sc = h->s_cmp;
     CU(cudaEventRecord(h->ev[0], sc));
+    const size_t rec = (size_t)h->ntr * h->F;  // doubles per record and level
+    // records of chunk c for the other ranks -> exchange -> ghost records of chunk c (stream s_comm)
+    auto halo = [&](int c) -> int {
+        const int k0 = h->chunk_k[c], k1 = h->chunk_k[c + 1];
+        const size_t rc = rec * (size_t)(k1 - k0);  // doubles per record in this chunk
+        at.k0 = k0;
+        at.k1 = k1;
+        at.sendbuf = h->d_sendbuf + (size_t)h->cfg.nsend * k0 * rec;
+        if (wxb_euler_edge_traces(at, h->n, sc) != 0) {
+            set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return WXB_ECUDA;
+        }
+        CU(cudaEventRecord(h->ev_packed_c[c], sc));
+        CU(cudaStreamWaitEvent(h->s_comm, h->ev_packed_c[c], 0));
+        double* stage = h->d_recv_stage + (size_t)h->cfg.nghost * k0 * rec;
+        NC(g_nccl.GroupStart());
+        for (int i = 0; i < h->n_send_peers; ++i)
+            NC(g_nccl.Send(at.sendbuf + (size_t)h->send_first[i] * rc, (size_t)h->send_count[i] * rc, 8 /* ncclFloat64 */, h->send_peer[i],
+                           h->nccl_comm, h->s_comm));
+        for (int i = 0; i < h->n_recv_peers; ++i)
+            NC(g_nccl.Recv(stage + (size_t)h->recv_first[i] * rc, (size_t)h->recv_count[i] * rc, 8, h->recv_peer[i], h->nccl_comm, h->s_comm));
+        NC(g_nccl.GroupEnd());
+        if (wxb_unpack_ghost(stage, h->d_trace + h->trace_local, h->cfg.nghost, (int)rec, k0, k1, h->cfg.nz, h->s_comm) != 0) {
+            set_err(h, "unpack kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return WXB_ECUDA;
+        }
+        CU(cudaEventRecord(h->ev_halo_c[c], h->s_comm));
+        return WXB_OK;
+    };
     auto traces = [&](int c) -> int {
         if (fused) return 0;  // the fused kernel extrapolates from the state itself
         if (nc > 1) {
@@ -935,9 +999,11 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
                 set_err(h, "trace kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
                 return WXB_ECUDA;
             }
+            if (dist && (r = halo(c)) != WXB_OK) return r;
             if (c == nc - 1) CU(cudaEventRecord(h->ev[1], sc));
         }
         if (c >= 1) {  // traces of chunks <= c are in flight: chunk c-1 has everything it reads
+            if (dist) CU(cudaStreamWaitEvent(sc, h->ev_halo_c[c < nc ? c : nc - 1], 0));  // ghost records of chunks <= c are in place
             if (maink(c - 1) != 0) {
                 set_err(h, "main kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
                 return WXB_ECUDA;
@@ -957,10 +1023,11 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     return WXB_OK;
 }
 
-// hosts entry points are for handles without remote neighbours; the advection-only short cut keeps the plain path
+// host entry points on a handle with remote neighbours need the library's own exchange (wxb_comm_init) and are then
+// collective like wxb_eval_dist; the advection-only short cut keeps the plain path
 static int host_ready(wxb_handle* h, bool* plain) {
-    if (h->cfg.nghost != 0) {
-        set_err(h, "handle has remote neighbours: use wxb_traces / exchange / wxb_finish");
+    if (has_remote(h) && !h->nccl_comm) {
+        set_err(h, "handle has remote neighbours: call wxb_comm_init first, or use wxb_traces / exchange / wxb_finish");
         return WXB_ESTATE;
     }
     *plain = h->cfg.equations == WXB_EQ_EULER3D && h->cfg.advection_only;

@@ -107,6 +107,9 @@ struct wxb_handle {
     int* d_clist;                       // elements of chunk 0, chunk 1, ...
     cudaStream_t s_in, s_cmp, s_out;
     cudaEvent_t ev_in[WXB_MAX_CHUNKS], ev_main[WXB_MAX_CHUNKS];
+    // multi-rank handles: the exchange runs chunk by chunk too (records of chunk c -> NCCL -> unpacked ghost records)
+    cudaEvent_t ev_packed_c[WXB_MAX_CHUNKS], ev_halo_c[WXB_MAX_CHUNKS];
+    double* d_recv_stage;       // ghost records as they arrive, chunk-major
     // one event triple per evaluation, in a ring: [0] start, [1] traces(+pack) done, [2] main done
     cudaEvent_t ev_ring[WXB_TIMING_RING][3];
     int ev_mode[WXB_TIMING_RING];
@@ -132,6 +135,7 @@ int wxb_sweep_configure(int n);
 void wxb_sweep_tile_shape(int n, int* tj, int* ti);
 int wxb_euler_sweep(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_euler_edge_traces(const EvalArgs& a, int n, cudaStream_t s);
+int wxb_unpack_ghost(const double* stage, double* ghost, int nghost, int rec, int k0, int k1, int nz, cudaStream_t s);
 void wxb_sw_tile_shape(int n, int* tj, int* ti);
 int wxb_sw_tile(const EvalArgs& a, int n, cudaStream_t s);
 int wxb_sw_tile_edge_traces(const EvalArgs& a, int n, cudaStream_t s);

@@ -262,6 +262,12 @@ class RhsB200:
         with torch.cuda.stream(stream):
             exchange(self.part, self._send_t, self._recv_t, self._rec, self.group)
 
+    def _host_entry_points(self):
+        """The library's host entry points (chunked upload / sweeps / download, csrc/wxb_api.cu: pipelined_eval) serve a
+        handle without remote neighbours, and a multi-rank handle once the library owns the exchange (init_comm): the
+        call is then collective over the ranks like every evaluation."""
+        return (self.part.nghost == 0 and self.part.nsend == 0) or bool(self._lib_comm)
+
     # ---- evaluation -------------------------------------------------------------------------------
     def _eval_device(self, q, v, rhs0, dt, eps, mode):
         torch = self._tm()
@@ -296,7 +302,7 @@ class RhsB200:
             self.retrieve_last_times()
         if isinstance(q, numpy.ndarray):
             a = self._as_host(q, "q")
-            if self.nranks != 1:  # halo exchange needs the split device path: H2D, evaluate, D2H
+            if not self._host_entry_points():  # torch-side exchange: H2D, evaluate, D2H
                 torch = self._tm()
                 qd = torch.from_numpy(a.reshape(-1)).to(f"cuda:{self.device_index}", non_blocking=True)
                 res = self._eval_device(qd, None, None, 0.0, 0.0, -1)
@@ -324,7 +330,7 @@ class RhsB200:
             raise ValueError(f"unknown JVP mode {mode!r} (complex-step is not available on this path)")
         if isinstance(Q, numpy.ndarray):
             q, v, r = self._as_host(Q, "Q"), self._as_host(vec, "vec"), self._as_host(rhs0, "rhs")
-            if self.nranks != 1:
+            if not self._host_entry_points():
                 torch = self._tm()
                 dev = f"cuda:{self.device_index}"
                 qd, vd, rd = (torch.from_numpy(x.reshape(-1)).to(dev, non_blocking=True) for x in (q, v, r))
@@ -350,7 +356,7 @@ class RhsB200:
         Krylov iteration: wx_factory/integrators/ros2.py:29)."""
         if mode not in ("fd", "rat"):
             raise ValueError(f"unknown JVP mode {mode!r} (complex-step is not available on this path)")
-        if isinstance(Q, numpy.ndarray) and self.nranks == 1:
+        if isinstance(Q, numpy.ndarray) and self._host_entry_points():
             a = self._as_host(Q, "Q")
             out = self._host_result()
             self._check(self._lib.wxb_linearize_host(self._h, a.ctypes.data, out.ctypes.data), "wxb_linearize_host")
@@ -431,7 +437,8 @@ def matvec_rat(vec, dt, Q, rhs, rhs_handle):
 
 class MatvecOpB200:
     """``MatvecOp`` (wx_factory/solvers/matvec.py:7-27: ``dtype``, ``shape``, ``size``, ``__call__(vec)``) for a
-    ``RhsB200``.  With host arrays on a single-rank handle the linearisation point (Q, rhs) is uploaded once -- at
+    ``RhsB200``.  With host arrays (single-rank handle, or a multi-rank one whose exchange the library owns) the
+    linearisation point (Q, rhs) is uploaded once -- at
     ``RhsB200.linearize`` or at the first application -- and kept on the device; the operator is then a snapshot of
     (Q, rhs) at that moment (the reference's closure would see later in-place changes of Q; its integrators build
     a new operator every step instead).  Device arrays and multi-rank handles go through ``RhsB200.jvp``."""
@@ -441,7 +448,7 @@ class MatvecOpB200:
         self.dtype, self.shape = Q.dtype, tuple(Q.shape)
         self.size = int(math.prod(self.shape))
         self._token = token
-        self._host = isinstance(Q, numpy.ndarray) and isinstance(rhs_vec, numpy.ndarray) and owner.nranks == 1
+        self._host = isinstance(Q, numpy.ndarray) and isinstance(rhs_vec, numpy.ndarray) and owner._host_entry_points()
 
     def matvec(self, vec):
         return self(vec)
