@@ -179,12 +179,14 @@ int wxb_eval_dist(wxb_handle* h, const double* q, const double* v, const double*
 
 /* Same as wxb_rhs / wxb_jvp with HOST buffers: H2D copy, kernels, D2H copy, synchronise.  For the 3-D Euler
  * equations the state moves in chunks of vertical levels on three streams, so that the upload of one chunk, the
- * kernels of the previous one and the download of the one before overlap (env WXB_HOST_CHUNKS, default 12;
+ * kernels of the previous one and the download of the one before overlap (env WXB_HOST_CHUNKS, default 24;
  * page-locked host buffers are needed for the copies to run asynchronously).
  * On a handle WITH remote neighbours these calls need wxb_comm_init first (WXB_ESTATE otherwise) and are collective
- * like wxb_eval_dist: on the fused Euler path the records other ranks need are formed and exchanged chunk by chunk
- * behind the uploads (the exchange of a chunk, the sweep of the previous one and the download of the one before
- * overlap); on the other paths the whole arrays go up, wxb_eval_dist runs, the whole result comes down. */
+ * like wxb_eval_dist: on the fused Euler path with up to two ranks the records other ranks need are formed and
+ * exchanged chunk by chunk behind the uploads (the exchange of a chunk, the sweep of the previous one and the
+ * download of the one before overlap); otherwise the whole arrays go up, wxb_eval_dist runs, the whole result comes
+ * down (env WXB_HOST_DIST=pipe|whole overrides the choice; with more ranks copying at once the measured boxes are
+ * bound by host bandwidth and the overlap buys nothing). */
 int wxb_rhs_host(wxb_handle* h, const double* q_host, double* dq_host);
 int wxb_jvp_host(wxb_handle* h, const double* q_host, const double* v_host, const double* rhs0_host, double dt,
                  double eps, int mode, double* out_host);

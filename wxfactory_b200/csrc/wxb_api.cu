@@ -835,7 +835,8 @@ static int pipe_setup(wxb_handle* h) {
     if (r != WXB_OK) return r;
     const bool euler = h->cfg.equations == WXB_EQ_EULER3D;
     const int nz = euler ? h->cfg.nz : 1;
-    int want = getenv("WXB_HOST_CHUNKS") ? atoi(getenv("WXB_HOST_CHUNKS")) : 12;
+    // measured at S2 s = 1 (24 levels), end-to-end step: 8 chunks 172 ms, 12 chunks 165 ms, 24 chunks 158 ms
+    int want = getenv("WXB_HOST_CHUNKS") ? atoi(getenv("WXB_HOST_CHUNKS")) : 24;
     if (want < 1) want = 1;
     if (want > WXB_MAX_CHUNKS) want = WXB_MAX_CHUNKS;
     h->nchunk = nz < want ? nz : want;
@@ -925,7 +926,12 @@ static int pipelined_eval(wxb_handle* h, double* d_q, const double* q_host, doub
     if (r != WXB_OK) return r;
     const bool fused = use_fused(h, jvp);
     const bool dist = has_remote(h);
-    if (dist && !(fused && euler && h->nchunk > 1))
+    // With more than two ranks copying at once the boxes this was measured on run out of HOST bandwidth (4 GPUs: 17-24
+    // GB/s per GPU and direction when all copy both ways, against 45-55 one way): overlapping the two directions then
+    // buys nothing and the pipeline's fill and drain cost ~20 %.  WXB_HOST_DIST=pipe|whole overrides.
+    const char* hd_env = getenv("WXB_HOST_DIST");
+    const bool dist_pipe = hd_env ? strcmp(hd_env, "pipe") == 0 : h->comm_nranks <= 2;
+    if (dist && !(fused && euler && h->nchunk > 1 && dist_pipe))
         return whole_array_dist_eval(h, d_q, q_host, d_v, v_host, d_r0, r0_host, dt, eps, mode, d_out, out_host);
     if (jvp && !h->d_qp && !fused) CU(cudaMalloc((void**)&h->d_qp, (size_t)wxb_state_size(h) * sizeof(double)));
     const int nc = h->nchunk;

@@ -69,7 +69,7 @@ struct EvalArgs {
     SlabTab st;
 };
 
-#define WXB_MAX_CHUNKS 16
+#define WXB_MAX_CHUNKS 64
 
 struct wxb_handle {
     wxb_config cfg;
