@@ -577,7 +577,7 @@ def run_b200(args):
         out = {
             "elements_per_panel": [nzq, nhq, nhq], "nodes": w.tiled.num_nodes, "dofs": w.tiled.num_dofs,
             "value": 2.0 * w.tiled.num_dofs * args.steps / (m * 1e-3), "unit": UNIT, "ms_per_step": m / args.steps,
-            "rhs_ms": er, "jvp_ms": ej,
+            "rhs_ms": er, "jvp_ms": ej, "kernel_path": w.rhs.path_name,
             "rhs_frac": b_rhs(n) * w.nodes_local / (er * 1e-3) / 1e9 / peak,
             "jvp_frac": b_jvp(n) * w.nodes_local / (ej * 1e-3) / 1e9 / peak,
             "parity": par,

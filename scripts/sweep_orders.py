@@ -45,7 +45,7 @@ def run(n, nh, nz, label, steps=20):
     hist, modes = rhs.timing_history(2 * steps)
     nodes = tiled.num_nodes
     t_r, t_j = hist[modes < 0][:, 2].mean() * 1e-3, hist[modes >= 0][:, 2].mean() * 1e-3
-    out = {"n": n, "shape": label, "elements_per_panel": [nz, nh, nh], "nodes": nodes,
+    out = {"n": n, "shape": label, "elements_per_panel": [nz, nh, nh], "nodes": nodes, "kernel_path": rhs.path_name,
            "rhs_ms": t_r * 1e3, "jvp_ms": t_j * 1e3,
            "rhs_gdof_s": 5 * nodes / t_r / 1e9, "jvp_gdof_s": 5 * nodes / t_j / 1e9,
            "rhs_frac_hbm": (360 + 96 / n) * nodes / t_r / 1e9 / PEAK, "jvp_frac_hbm": (440 + 96 / n) * nodes / t_j / 1e9 / PEAK,

@@ -232,8 +232,22 @@ int build(wxb_handle* h, const wxb_config* cfg, const wxb_static_arrays* A) {
     // a mixed mode (RHS fused, JVP pair) was measured faster and broke the Krylov iteration counts of Epi(2) on dcmip31.
     {
         const char* pe = getenv(euler ? "WXB_EULER_PATH" : "WXB_SW_PATH");
-        // default per order: the path that measured faster (profiles/r02_sweep_orders.jsonl, r02_order_variants.log)
-        const bool fused_default = euler ? WXB_SWEEP_DEFAULT(n) : true;
+        // default per order and size: the path that measured faster (profiles/r02_sweep_orders.jsonl, r02_order_variants.log)
+        bool fused_default = euler ? WXB_SWEEP_DEFAULT(n) : true;
+        if (euler && fused_default) {
+            // The sweep kernel gives a block a tile of columns and walks up it: a handle with few tiles cannot fill the
+            // GPU for long (the reference authors' 60^3-node benchmark shape at n = 4 is 384 tiles of 15 levels for
+            // 296 resident blocks: 0.242 ms against 0.157 ms on the element-parallel pair).  Below 4 full waves of
+            // blocks the pair serves the handle.  (Blocks per SM as compiled in euler_sweep.cu: WXB_SW_MINB<n>.)
+            int tj = 1, ti = 1;
+            wxb_sweep_tile_shape(n, &tj, &ti);
+            long long tiles = 0;
+            for (int s = 0; s < cfg->nslabs; ++s) tiles += (long long)((st.ny[s] + tj - 1) / tj) * ((nx + ti - 1) / ti);
+            const int blocks_per_sm = n == 2 ? 4 : (n == 6 ? 1 : 2);
+            int sms = 148;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+            if (tiles < 4LL * sms * blocks_per_sm) fused_default = false;
+        }
         h->split = pe ? strcmp(pe, "split") == 0 : !fused_default;
         h->sweep = !h->split;
     }
