@@ -542,6 +542,10 @@ def run_b200(args):
                     if world == 1
                     else "the same two calls on every rank (collective): level chunks up, the records other ranks need formed and exchanged "
                     "chunk by chunk over NCCL inside the library, sweeps and downloads behind them (wxb_api.cu: pipelined_eval)"
+                    if world <= 2 and os.environ.get("WXB_HOST_DIST", "pipe") == "pipe" or os.environ.get("WXB_HOST_DIST") == "pipe"
+                    else "the same two calls on every rank (collective): whole arrays up, wxb_eval_dist (exchange overlapped with the inner "
+                    "tiles), whole result down -- with more than two GPUs copying at once the host side of the box is the limit and "
+                    "overlapping the two directions buys nothing (DESIGN section 6; WXB_HOST_DIST=pipe forces the level pipeline)"
                 ),
             },
             "gpu_launches": int(launches),

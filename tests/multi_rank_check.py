@@ -30,12 +30,16 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     cond = json.load(open(os.path.join(ROOT, "tests", "golden", "conditioning.json")))["cases"]
     ok = True
-    for name in ["dcmip31_n4", "dcmip21", "dcmip31", "case6", "galewsky"]:
+    # handles this small default to the traces + main pair (wxb_api.cu: build): every case runs on BOTH kernel paths,
+    # forced through the environment, which is read when a handle is created
+    for name, path in [(n_, p_) for n_ in ["dcmip31_n4", "dcmip21", "dcmip31", "case6", "galewsky"] for p_ in ("fused", "pair")]:
         prob, ex = load_problem(os.path.join(ROOT, "tests", "golden", name + ".npz"))
         if (6 * prob.nh) % world:
-            if rank == 0:
+            if rank == 0 and path == "fused":
                 print(f"{name}: 6*nh = {6 * prob.nh} rows do not split over {world} ranks, skipped")
             continue
+        os.environ["WXB_EULER_PATH"] = "sweep" if path == "fused" else "split"
+        os.environ["WXB_SW_PATH"] = "tile" if path == "fused" else "split"
         dt = float(ex["dt"])
         rhs = RhsB200(prob, nranks=world, rank=rank, device=local)
         q = torch.from_numpy(rhs.local_state(ex["Q0"])).to(dev)
@@ -84,9 +88,11 @@ def main():
             tol = max(1e-12, 2 * cond[name]["ref_rounding"])
             good = same and err <= tol and host_same
             ok = ok and good
-            print(f"{name}: {world} ranks vs 1 rank bit-identical={same}; host entry points (both modes) == device path on every rank: {host_same}; vs reference {err:.2e} (bound {tol:.1e}) -> {'ok' if good else 'FAIL'}", flush=True)
+            print(f"{name} [{rhs.path_name}]: {world} ranks vs 1 rank bit-identical={same}; host entry points (both modes) == device path on every rank: {host_same}; vs reference {err:.2e} (bound {tol:.1e}) -> {'ok' if good else 'FAIL'}", flush=True)
         rhs.close()
         dist.barrier()
+    os.environ.pop("WXB_EULER_PATH", None)
+    os.environ.pop("WXB_SW_PATH", None)
     ok = steps_check(rank, world, local, dev) and ok
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, 0)

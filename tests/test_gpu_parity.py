@@ -219,14 +219,18 @@ def test_other_kernel_paths_match_too(env):
     """A handle runs ONE kernel path, chosen at create: the fused kernel (Euler: csrc/euler_sweep.cu, default at the orders
     where it measured faster, n = 2 and 4; shallow water: csrc/sw_tile.cu) or the traces + main pair (csrc/euler3d.cu,
     csrc/sw2d.cu).  WXB_EULER_PATH / WXB_SW_PATH force one for every order, per process: run the device-path, JVP and
-    host-pipeline parity cases again in a child process with each, so that both paths are checked at every order."""
+    host-pipeline and perturbed-state parity cases and the integrator trajectories (Krylov iteration counts of the
+    reference) again in a child process with each, so that both paths are checked at every order -- the golden grids are
+    small, and a small handle defaults to the pair (wxb_api.cu: build)."""
     import subprocess
     import sys
 
     here = os.path.abspath(__file__)
+    steps = os.path.join(os.path.dirname(here), "test_gpu_steps.py")
     r = subprocess.run(
-        [sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k", "device_path or jvp_matches or host_pipeline"],
-        env=dict(os.environ, **env), capture_output=True, text=True, timeout=600,
+        [sys.executable, "-m", "pytest", here, steps, "-q", "-x", "-m", "gpu", "-k",
+         "device_path or jvp_matches or host_pipeline or perturbed_states or steps_follow_reference or tvdrk3_class_drift"],
+        env=dict(os.environ, **env), capture_output=True, text=True, timeout=900,
     )
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
