@@ -50,41 +50,81 @@ def load_state(input_file_name):
     return state, version, content
 
 
-def gather_state(rhs, local, group=None):
-    """Flat local state of every rank (numpy or CUDA tensor) -> global ``prob.state_shape`` numpy array on rank 0
-    (None elsewhere).  ``rhs``: this rank's ``RhsB200`` (knows the problem and the partition)."""
+def _peer_partition(rhs, r):
     from .partition import build_partition
 
     prob = rhs.prob
-    loc = local.detach().cpu().numpy() if hasattr(local, "detach") else numpy.asarray(local)
-    loc = loc.reshape(-1)
-    if rhs.nranks == 1:
-        return scatter_back(prob, rhs.part, loc, numpy.empty(prob.state_shape))
+    if r == rhs.rank:
+        return rhs.part
+    euler = prob.equations == "euler"
+    return build_partition(prob.nh, prob.nz if euler else 1, prob.n, prob.bnd_sn, prob.bnd_we, nranks=rhs.nranks, rank=r,
+                           num_var=rhs.num_trace, nfaces=6 if euler else 4, trace_layout="element" if euler else "field")
+
+
+def _wire(group):
+    """Where point-to-point tensors must live for the group's backend: NCCL moves device memory, gloo host memory."""
+    import torch
     import torch.distributed as dist
 
-    pieces = [None] * rhs.nranks if rhs.rank == 0 else None
-    dist.gather_object(loc, pieces, dst=0, group=group)
+    if dist.get_backend(group) == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def _global_rank(group, r):
+    import torch.distributed as dist
+
+    return r if group is None else dist.get_global_rank(group, r)
+
+
+def gather_state(rhs, local, group=None):
+    """Flat local state of every rank (numpy or CUDA tensor) -> global ``prob.state_shape`` numpy array on rank 0
+    (None elsewhere).  ``rhs``: this rank's ``RhsB200`` (knows the problem and the partition).  The pieces travel one
+    at a time as float64 tensors, point to point (ProcessTopology.gather_cube, process_topology.py:444-470, moves
+    arrays, not pickles): rank 0 holds one piece besides the result, whatever the number of ranks."""
+    prob = rhs.prob
+    if rhs.nranks == 1:
+        loc = local.detach().cpu().numpy() if hasattr(local, "detach") else numpy.asarray(local)
+        return scatter_back(prob, rhs.part, loc.reshape(-1), numpy.empty(prob.state_shape))
+    import torch
+    import torch.distributed as dist
+
+    wire = _wire(group)
+    mine = local.detach() if hasattr(local, "detach") else torch.from_numpy(numpy.ascontiguousarray(local, dtype=numpy.float64))
+    mine = mine.reshape(-1).to(wire)
     if rhs.rank != 0:
+        dist.send(mine.contiguous(), dst=_global_rank(group, 0), group=group)
         return None
     out = numpy.empty(prob.state_shape)
-    euler = prob.equations == "euler"
-    for r, piece in enumerate(pieces):
-        part = rhs.part if r == rhs.rank else build_partition(
-            prob.nh, prob.nz if euler else 1, prob.n, prob.bnd_sn, prob.bnd_we, nranks=rhs.nranks, rank=r,
-            num_var=rhs.num_trace, nfaces=6 if euler else 4, trace_layout="element" if euler else "field")
-        scatter_back(prob, part, piece, out)
+    scatter_back(prob, rhs.part, mine.cpu().numpy(), out)
+    buf = torch.empty_like(mine)  # 6 nh rows split evenly: every rank's piece has this rank's size
+    for r in range(1, rhs.nranks):
+        dist.recv(buf, src=_global_rank(group, r), group=group)
+        scatter_back(prob, _peer_partition(rhs, r), buf.cpu().numpy(), out)
     return out
 
 
 def scatter_state(rhs, global_state, group=None):
-    """Global state on rank 0 (ignored elsewhere) -> this rank's flat local numpy state."""
+    """Global state on rank 0 (ignored elsewhere) -> this rank's flat local numpy state.  Rank 0 cuts every rank's piece
+    out of the global array and sends only that (ProcessTopology.distribute_cube, process_topology.py:472-539)."""
     if rhs.nranks == 1:
         return rhs.local_state(global_state)
+    import torch
     import torch.distributed as dist
 
-    box = [numpy.asarray(global_state) if rhs.rank == 0 else None]
-    dist.broadcast_object_list(box, src=0, group=group)
-    return rhs.local_state(box[0])
+    wire = _wire(group)
+    if rhs.rank == 0:
+        for r in range(1, rhs.nranks):
+            tiled = getattr(rhs.prob, "local_state", None)  # synthetic tiled problems cut their own pieces (rhs.local_state)
+            part = _peer_partition(rhs, r)
+            piece = tiled(part, global_state) if tiled is not None else local_state(rhs.prob, part, global_state)
+            piece = numpy.ascontiguousarray(piece, dtype=numpy.float64).reshape(-1)
+            dist.send(torch.from_numpy(piece).to(wire), dst=_global_rank(group, r), group=group)
+        return rhs.local_state(global_state)
+    size = getattr(rhs, "size", None) or int(numpy.prod(rhs.prob.state_shape)) // rhs.nranks  # 6 nh rows split evenly
+    buf = torch.empty(int(size), dtype=torch.float64, device=wire)
+    dist.recv(buf, src=_global_rank(group, 0), group=group)
+    return buf.cpu().numpy()
 
 
 def write_restart(rhs, local, config_content, output_dir, step_id, dt, group=None):
