@@ -118,10 +118,11 @@ def test_reference_tvdrk3_on_the_b200_surface_is_bit_identical(ref, bundle_class
     assert numpy.array_equal(QN, g["QN"])
 
 
-@pytest.mark.parametrize("case", ["ros2_dcmip21", "epi2_dcmip31"])
+@pytest.mark.parametrize("case", ["ros2_dcmip21", "epi2_dcmip31", "epi4_dcmip21", "epi3_case6"])
 def test_reference_implicit_and_exponential_integrators_on_the_b200_surface(ref, bundle_class, case):
     """The reference's Ros2 + fgmres (wx_factory/integrators/ros2.py:24-81: MatvecOpRat(dt, Q, rhs, rhs_handle)) and
-    Epi(2) + kiops (wx_factory/integrators/epi.py:81-360: matvec_fun(v, dt, Q, rhs, rhs_handle, 'fd') in a closure), both
+    Epi(2) + kiops (wx_factory/integrators/epi.py:81-360: matvec_fun(v, dt, Q, rhs, rhs_handle, 'fd') in a closure), the
+    multistep Epi(4) + kiops (two previous steps in its history) and Epi(3) + pmex on the shallow-water case6 as shipped, all
     imported unchanged, with the B200 versions of MatvecOpRat / matvec_fun in their module namespaces -- the one-line
     change INTEGRATION.md describes -- and RhsBundleB200(...).full as rhs_handle on every rank.  Same Krylov iteration
     counts as the reference's own run in every step and the same final state to the solver tolerance."""
@@ -158,6 +159,8 @@ def test_reference_implicit_and_exponential_integrators_on_the_b200_surface(ref,
     assert all(list(its) == list(g["iterations"]) for _, its in res)
     err = numpy.linalg.norm(QN - g["QN"]) / numpy.linalg.norm(g["QN"])
     print(f"{case}: drift vs the reference's own run {err:.2e}")
-    assert err <= 1e-9
+    # case6 / PMEX amplifies a 2e-16 input perturbation to 1.4e-8 after 4 steps (tests/test_integrators_host.py): its bound
+    # is the solver tolerance
+    assert err <= (1e-7 if case == "epi3_case6" else 1e-9)
     calls = bundles[0].owner._lib.calls
     assert "jvp_host" in calls  # the fused JVP entry served the Krylov iterations, not the generic formula
