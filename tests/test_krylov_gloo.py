@@ -123,3 +123,47 @@ def test_two_rank_krylov_and_state_bridge():
     ok = mp.get_context("spawn").Array("i", [0] * world)
     mp.spawn(_worker, args=(world, port, ok), nprocs=world, join=True)
     assert list(ok) == [1] * world
+
+
+def _bridge_worker(rank, world, port, members, ok):
+    """State bridge inside a (sub)group: ranks outside `members` only take part in creating the group."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        group = dist.new_group(ranks=members) if len(members) < world else None
+        if rank not in members:
+            ok[rank] = 1
+            return
+        gr, gw = members.index(rank), len(members)
+        prob, ex = load_problem(os.path.join(HERE, "golden", "dcmip31.npz"))
+        part = build_partition(prob.nh, prob.nz, prob.n, prob.bnd_sn, prob.bnd_we, nranks=gw, rank=gr, num_var=6, nfaces=6, trace_layout="element")
+        rhs = types.SimpleNamespace(prob=prob, part=part, nranks=gw, rank=gr, num_trace=6, local_state=lambda Q: local_state(prob, part, Q))
+        mine = local_state(prob, part, ex["Q0"])
+        total = state_io.gather_state(rhs, torch.from_numpy(mine), group)  # a tensor, as the integrators hold it
+        good = (total is None) if gr else bool(numpy.array_equal(total, ex["Q0"].reshape(prob.state_shape)))
+        back = state_io.scatter_state(rhs, total, group)
+        good = good and bool(numpy.array_equal(back, mine)) and back.dtype == numpy.float64
+        ok[rank] = int(good)
+    finally:
+        dist.destroy_process_group()
+
+
+def _run_bridge(world, members):
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ok = mp.get_context("spawn").Array("i", [0] * world)
+    mp.spawn(_bridge_worker, args=(world, port, members, ok), nprocs=world, join=True)
+    assert list(ok) == [1] * world
+
+
+def test_state_bridge_moves_one_piece_per_rank_over_four_ranks():
+    """gather_state / scatter_state send float64 tensors point to point, one rank's rows at a time
+    (ProcessTopology.gather_cube / distribute_cube, process_topology.py:444-539): 4 ranks, 1.5 panels each."""
+    _run_bridge(4, [0, 1, 2, 3])
+
+
+def test_state_bridge_inside_a_subgroup():
+    """The group's rank numbers are translated to global ones for the point-to-point calls: ranks 1 and 2 of a
+    3-process job form the group, rank 0 of the job is not part of it."""
+    _run_bridge(3, [1, 2])
